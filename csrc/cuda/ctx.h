@@ -1,0 +1,82 @@
+// ctx.h -- device-visible description of one rank's part of the solve.
+//
+// One `RankCtx` describes the local block of a rank, its arrays, its four neighbours and the
+// cross-rank reduction workspace.  A real multi-GPU run has one context per process/GPU with peer
+// pointers obtained through CUDA IPC; a single-GPU "virtual rank" run (tests, decomposition checks)
+// places several contexts on one device and one cooperative launch serves all of them.
+//
+// Replaces, in one structure, what the reference passes around as loose arguments: the local ranges
+// (S4:706-709), the eight device arrays (S4:737-748), the neighbour ranks (S4:341-344) and the
+// partial-sum buffer (S4:766-768).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+#include "../core/decomp.h"
+#include "../core/problem.h"
+
+namespace pb {
+
+constexpr int kMaxRanks = 16;
+constexpr int kMaxCtas = 1024;      // per rank
+constexpr int kRedValues = 2;       // doubles carried by one cross-rank reduction
+constexpr int kSlotWords = 4;       // 2 doubles -> 4 (payload32 | seq32) words
+
+// Arena layout (identical on every rank, so a peer needs only the arena base address).
+constexpr size_t kCtlOffset = 0;                   // Control
+constexpr size_t kSlotsOffset = 4096;              // [2 parities][kMaxRanks][kSlotWords] u64
+constexpr size_t kArriveOffset = 8192;             // arrival counter (u32) + padding
+constexpr int kPartialStride = 8;                  // doubles per CTA in the partials area
+constexpr size_t kPartialsOffset = 16384;          // [kMaxCtas][kPartialStride] doubles
+constexpr size_t kHeaderBytes = 131072;            // arrays start here; r is the first array
+
+// Scalars of the iteration, status and device-side timers.  Lives at the start of the arena.
+struct Control {
+  // iteration state
+  double zr_old, alpha, beta, denom, diff2, zr_new, diff_norm;
+  double red[4];             // staging for step-wise reductions (local sums, then global sums)
+  int iter;                  // index of the current / final iteration
+  int status;                // PB_STATUS_*
+  unsigned int red_seq;      // sequence number of the last cross-rank reduction (persists across solves)
+  unsigned int arrive_base;  // value of the arrival counter at the start of the next reduction
+  int cur;                   // which p buffer holds the current direction
+  int pad0;
+  // options
+  double delta;
+  long long max_iter;
+  int norm;
+  int pad1;
+  unsigned long long watchdog_ns;  // 0 = default
+  // device timers (ns, accumulated by CTA 0 of the persistent kernel)
+  unsigned long long t_ab, t_c, t_red1, t_red2, t_init, t_total;
+  // error report partials {sum e^2 in D, sum e^2 all, max |e|, max w, nodes in D}
+  double err[5];
+};
+
+struct RankCtx {
+  Grid g;
+  int i0, j0, nx, ny, pitch;
+  int rank, nranks;
+  int nbr[4];  // neighbour ranks (x-, x+, y-, y+), -1 at the boundary of Omega
+  // local arrays, all (nx+2) x pitch
+  double *w, *r, *p[2], *Ap, *a, *b, *D;
+  // neighbour r arrays as seen from this GPU (peer mapped), with their row pitch and extents
+  double* nbr_r[4];
+  int nbr_pitch[4];
+  int nbr_nx[4], nbr_ny[4];
+  // reduction workspace (local) and every rank's slot area as seen from this GPU
+  double* partials;
+  unsigned int* arrive;
+  unsigned long long* slots;
+  unsigned long long* peer_slots[kMaxRanks];
+  Control* ctl;
+  // tiling of the block for the stencil phase
+  int tiles_x, tiles_y;
+};
+
+constexpr int kTileX = 32;  // rows per stencil tile
+constexpr int kTileY = 64;  // columns per stencil tile
+
+inline size_t arena_bytes(const LocalBlock& b) { return kHeaderBytes + 8 * b.elems() * sizeof(double); }
+
+}  // namespace pb

@@ -1,0 +1,45 @@
+// launch.h -- host-callable launchers of the device kernels (one declaration per kernel family).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "ctx.h"
+
+namespace pb {
+
+// K0 (assemble.cu): a, b, D, r = B, w = 0, p = 0, Ap = 0 on the block and its ring.
+cudaError_t launch_assemble(const RankCtx* d_ctx, const RankCtx& h_ctx, cudaStream_t stream);
+// error report partials -> Control::err (assemble.cu)
+cudaError_t launch_error_report(const RankCtx* d_ctx, const RankCtx& h_ctx, cudaStream_t stream);
+// gather the owned nodes of w into a dense (nx x ny) buffer with row stride `ld` (assemble.cu)
+cudaError_t launch_gather_interior(const double* w, int nx, int ny, int pitch, double* out, long long ld,
+                                   cudaStream_t stream);
+
+// KP (persistent.cu)
+size_t persistent_smem_bytes();
+int persistent_max_ctas_per_sm(bool exact);
+cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, bool exact, cudaStream_t stream);
+
+// step-wise kernels (step_kernels.cu); every kernel returns immediately when Control::status is not
+// PB_STATUS_RUNNING, so the host may enqueue iterations ahead of the stop test.
+enum StepPhase : int { kStepInit = 0, kStepAlpha = 1, kStepBeta = 2 };
+cudaError_t launch_step_begin(const RankCtx* d_ctx, cudaStream_t stream);  // status = RUNNING, iter = 0
+cudaError_t launch_step_dot_zr(const RankCtx* d_ctx, const RankCtx& h_ctx, cudaStream_t stream);
+cudaError_t launch_step_stencil(const RankCtx* d_ctx, const RankCtx& h_ctx, bool fuse_p, bool exact,
+                                cudaStream_t stream);
+cudaError_t launch_step_update(const RankCtx* d_ctx, const RankCtx& h_ctx, bool fuse_p, cudaStream_t stream);
+cudaError_t launch_step_update_p(const RankCtx* d_ctx, const RankCtx& h_ctx, cudaStream_t stream);
+// local partial sums -> Control::red[0..1]
+cudaError_t launch_step_reduce_local(const RankCtx* d_ctx, const RankCtx& h_ctx, int nvalues, cudaStream_t stream);
+// Control::red (global sums) -> alpha / beta / stop decision
+cudaError_t launch_step_scalars(const RankCtx* d_ctx, int phase, cudaStream_t stream);
+// pack / unpack the four edges of p for a library (NCCL / gloo) halo exchange
+cudaError_t launch_pack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, double* sendbuf, int stride,
+                              cudaStream_t stream);
+cudaError_t launch_unpack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, const double* recvbuf, int stride,
+                                cudaStream_t stream);
+
+// TMA variant of phase AB (tma_stencil.cu)
+cudaError_t launch_step_stencil_tma(const RankCtx* d_ctx, const RankCtx& h_ctx, const void* tensor_maps, bool exact,
+                                    cudaStream_t stream);
+
+}  // namespace pb

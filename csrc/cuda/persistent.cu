@@ -1,0 +1,176 @@
+// persistent.cu -- KP: the whole PCG iteration loop as one cooperative, persistent kernel.
+//
+// Replaces the host loop of the reference (S4:846-942: 6 kernel launches, 6 cudaDeviceSynchronize,
+// 3 x 256 KiB D2H, up to 8 halo memcpys, 4 MPI_Sendrecv and 3 MPI_Allreduce per iteration) by
+//
+//   loop:  phase AB  ->  cross-rank sum {(Ap,p)}            -> alpha
+//          phase C   ->  cross-rank sum {sum dw^2, (z,r)}   -> stop test, beta
+//
+// with alpha, beta and the stop decision computed redundantly (and bit-identically) by every CTA of
+// every rank.  Halo data (the neighbour's new r on our ring) is stored by the neighbour during its
+// phase C and becomes visible through the release/acquire chain of the second reduction, so an
+// iteration has exactly two cross-GPU synchronisation points and no separate halo exchange.
+//
+// One launch serves `nvirt` rank contexts: blockIdx.x / ctas_per_rank selects the context.  Real
+// multi-GPU runs use nvirt = 1 per process; tests place several virtual ranks on one GPU, where the
+// cooperative launch guarantees that all CTAs that wait for each other are co-resident.
+#include <cooperative_groups.h>
+
+#include "launch.h"
+#include "phases.cuh"
+
+namespace pb {
+
+template <bool EXACT>
+__global__ void __launch_bounds__(kThreads, 1)
+pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
+  __shared__ RankCtx c;
+  __shared__ double s_red[80];
+  extern __shared__ double s_tile[];
+
+  const int vrank = blockIdx.x / ctas_per_rank;
+  const int cta = blockIdx.x - vrank * ctas_per_rank;
+  const int ncta = ctas_per_rank;
+  {
+    const int* src = reinterpret_cast<const int*>(ctxs + vrank);
+    int* dst = reinterpret_cast<int*>(&c);
+    for (int i = threadIdx.x; i < (int)(sizeof(RankCtx) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+
+  Control* ctl = c.ctl;
+  const int ntiles = c.tiles_x * c.tiles_y;
+  const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
+  const bool timing = (cta == 0 && threadIdx.x == 0);
+
+  // Launch-time state.  red_seq persists across launches so that slot contents left over from an
+  // earlier solve can never be mistaken for a value of this one; the arrival counter is zeroed by the
+  // host before the launch.
+  unsigned int seq = ctl->red_seq;
+  unsigned int arrive_target = 0;
+  const double delta = ctl->delta;
+  const long long max_iter = ctl->max_iter;
+  const int norm = ctl->norm;
+  const double h1h2 = c.g.h1h2;
+
+  unsigned long long t_prev = timing ? globaltimer_ns() : 0ull, t_start = t_prev;
+  unsigned long long t_ab = 0, t_c = 0, t_r1 = 0, t_r2 = 0, t_init = 0;
+#define PB_STAMP(acc)                           \
+  if (timing) {                                 \
+    const unsigned long long now_ = globaltimer_ns(); \
+    acc += now_ - t_prev;                       \
+    t_prev = now_;                              \
+  }
+
+  // ---- init: zr_old = (D^-1 r, r) ----
+  double zr_old;
+  {
+    double v[1] = {0.0};
+    for (int t = cta; t < ntiles; t += ncta) v[0] += dot_zr_tile(c, t);
+    ++seq;
+    arrive_target += ncta;
+    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+    if (!rr.ok) {
+      if (threadIdx.x == 0 && cta == 0) {
+        ctl->status = PB_STATUS_WATCHDOG;
+        ctl->red_seq = seq;
+      }
+      return;
+    }
+    zr_old = rr.v[0] * h1h2;
+  }
+  PB_STAMP(t_init);
+
+  int cur = 0;
+  double beta = 0.0, alpha = 0.0, denom = 0.0, diff_norm = 0.0;
+  int status = PB_STATUS_MAXITER;
+  long long k = 0;
+  for (k = 1; k <= max_iter; ++k) {
+    const double* pin = c.p[cur];
+    double* pout = c.p[cur ^ 1];
+    // ---- phase AB ----
+    {
+      double v[1] = {0.0};
+      for (int t = cta; t < ntiles; t += ncta) v[0] += phase_ab_tile<true, EXACT>(c, t, beta, pin, pout, s_tile);
+      PB_STAMP(t_ab);
+      ++seq;
+      arrive_target += ncta;
+      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+      PB_STAMP(t_r1);
+      if (!rr.ok) {
+        status = PB_STATUS_WATCHDOG;
+        break;
+      }
+      denom = rr.v[0] * h1h2;
+    }
+    if (fabs(denom) < kBreakdownTol) {
+      status = PB_STATUS_BREAKDOWN;
+      break;
+    }
+    alpha = zr_old / denom;
+    // ---- phase C ----
+    double zr_new;
+    {
+      double v[2] = {0.0, 0.0};
+      for (int t = cta; t < ntiles; t += ncta) phase_c_tile(c, t, alpha, pout, v[0], v[1]);
+      PB_STAMP(t_c);
+      ++seq;
+      arrive_target += ncta;
+      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, has_nbr);
+      PB_STAMP(t_r2);
+      if (!rr.ok) {
+        status = PB_STATUS_WATCHDOG;
+        break;
+      }
+      diff_norm = norm == PB_NORM_WEIGHTED ? sqrt(rr.v[0] * h1h2) : sqrt(rr.v[0]);
+      zr_new = rr.v[1] * h1h2;
+    }
+    cur ^= 1;
+    if (diff_norm < delta) {
+      status = PB_STATUS_CONVERGED;
+      break;
+    }
+    beta = zr_new / zr_old;
+    zr_old = zr_new;
+  }
+  if (k > max_iter) k = max_iter;
+
+  if (cta == 0 && threadIdx.x == 0) {
+    ctl->iter = (int)k;
+    ctl->status = status;
+    ctl->diff_norm = diff_norm;
+    ctl->alpha = alpha;
+    ctl->beta = beta;
+    ctl->denom = denom;
+    ctl->zr_old = zr_old;
+    ctl->cur = cur;
+    ctl->red_seq = seq;
+    ctl->t_ab = t_ab;
+    ctl->t_c = t_c;
+    ctl->t_red1 = t_r1;
+    ctl->t_red2 = t_r2;
+    ctl->t_init = t_init;
+    ctl->t_total = globaltimer_ns() - t_start;
+  }
+#undef PB_STAMP
+}
+
+size_t persistent_smem_bytes() { return sizeof(double) * kSmemTile; }
+
+int persistent_max_ctas_per_sm(bool exact) {
+  int n = 0;
+  if (exact)
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pcg_persistent_kernel<true>, kThreads, persistent_smem_bytes());
+  else
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pcg_persistent_kernel<false>, kThreads, persistent_smem_bytes());
+  return n;
+}
+
+cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, bool exact, cudaStream_t stream) {
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank};
+  const dim3 grid(nvirt * ctas_per_rank), block(kThreads);
+  const void* fn = exact ? (const void*)pcg_persistent_kernel<true> : (const void*)pcg_persistent_kernel<false>;
+  return cudaLaunchCooperativeKernel(fn, grid, block, args, persistent_smem_bytes(), stream);
+}
+
+}  // namespace pb

@@ -1,0 +1,126 @@
+// solver.cu -- see solver.h.
+#include "solver.h"
+
+#include <algorithm>
+#include <cstddef>
+#include <cstring>
+
+#include "../api/error.h"
+#include "../cuda/launch.h"
+
+namespace pb {
+
+static_assert(offsetof(Control, max_iter) - offsetof(Control, delta) == offsetof(DeviceOptions, max_iter),
+              "DeviceOptions must mirror the option block of Control");
+static_assert(offsetof(Control, watchdog_ns) - offsetof(Control, delta) == offsetof(DeviceOptions, watchdog_ns),
+              "DeviceOptions must mirror the option block of Control");
+static_assert(sizeof(Control) <= kSlotsOffset, "Control overflows its page");
+static_assert(2 * kMaxRanks * kSlotWords * 8 <= kArriveOffset - kSlotsOffset, "slot area overflows");
+static_assert(kMaxCtas * kPartialStride * 8 <= kHeaderBytes - kPartialsOffset, "partials overflow");
+
+Solver::Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int device)
+    : grid_(make_grid(M, N)), pg_{Px, Py}, first_rank_(first_rank), device_(device) {
+  if (M < 2 || N < 2) throw std::runtime_error("Solver: M and N must be >= 2");
+  if (Px < 1 || Py < 1 || Px * Py > kMaxRanks) throw std::runtime_error("Solver: process grid must have 1..16 ranks");
+  if (Px > M - 1 || Py > N - 1) throw std::runtime_error("Solver: more blocks than interior nodes along an axis");
+  if (first_rank < 0 || nlocal < 1 || first_rank + nlocal > Px * Py)
+    throw std::runtime_error("Solver: local rank range outside the process grid");
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  PB_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_));
+  peer_base_.assign(nranks(), nullptr);
+  for (int l = 0; l < nlocal; ++l) {
+    blocks_.push_back(make_local_block(M, N, pg_, first_rank + l));
+    char* base = nullptr;
+    const size_t bytes = arena_bytes(blocks_.back());
+    PB_CUDA_CHECK(cudaMalloc(&base, bytes));
+    PB_CUDA_CHECK(cudaMemset(base, 0, bytes));
+    arenas_.push_back(base);
+    peer_base_[first_rank + l] = base;
+  }
+  PB_CUDA_CHECK(cudaMalloc(&dctx_, sizeof(RankCtx) * nlocal));
+  PB_CUDA_CHECK(cudaMallocHost(&pinned_opts_, sizeof(DeviceOptions)));
+  PB_CUDA_CHECK(cudaMallocHost(&pinned_ctl_, sizeof(Control) * nlocal));
+  for (auto& e : ev_) PB_CUDA_CHECK(cudaEventCreate(&e));
+  PB_CUDA_CHECK(cudaDeviceSynchronize());
+}
+
+Solver::~Solver() {
+  cudaSetDevice(device_);
+  cudaDeviceSynchronize();
+  for (void* p : opened_ipc_) cudaIpcCloseMemHandle(p);
+  for (char* a : arenas_) cudaFree(a);
+  if (dctx_) cudaFree(dctx_);
+  if (pinned_opts_) cudaFreeHost(pinned_opts_);
+  if (pinned_ctl_) cudaFreeHost(pinned_ctl_);
+  for (auto& e : ev_) cudaEventDestroy(e);
+}
+
+double* Solver::array(int l, int which) const {
+  if (which < 0 || which > 7) throw std::runtime_error("Solver::array: bad index");
+  // arena order: r, w, p0, p1, Ap, a, b, D  (r first so that peers find it at a fixed offset)
+  static const int order[8] = {1, 0, 2, 3, 4, 5, 6, 7};  // which -> slot
+  return reinterpret_cast<double*>(arenas_[l] + kHeaderBytes) + (size_t)order[which] * blocks_[l].elems();
+}
+
+void Solver::ipc_handle(int l, void* out64) const {
+  cudaIpcMemHandle_t h;
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  PB_CUDA_CHECK(cudaIpcGetMemHandle(&h, arenas_[l]));
+  static_assert(sizeof(h) == 64, "unexpected IPC handle size");
+  std::memcpy(out64, &h, 64);
+}
+
+void Solver::open_peer(int rank, const void* handle64) {
+  if (rank < 0 || rank >= nranks()) throw std::runtime_error("open_peer: bad rank");
+  if (rank >= first_rank_ && rank < first_rank_ + nlocal()) return;  // local
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle64, 64);
+  void* base = nullptr;
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  PB_CUDA_CHECK(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+  opened_ipc_.push_back(base);
+  peer_base_[rank] = base;
+}
+
+void Solver::set_peer_base(int rank, void* base) {
+  if (rank < 0 || rank >= nranks()) throw std::runtime_error("set_peer_base: bad rank");
+  peer_base_[rank] = base;
+}
+
+void Solver::finalize() {
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  for (int rk = 0; rk < nranks(); ++rk)
+    if (!peer_base_[rk]) throw std::runtime_error("Solver::finalize: arena of rank " + std::to_string(rk) + " unknown");
+  hctx_.clear();
+  for (int l = 0; l < nlocal(); ++l) {
+    const LocalBlock& b = blocks_[l];
+    RankCtx c;
+    std::memset(&c, 0, sizeof(c));
+    c.g = grid_;
+    c.i0 = b.i0, c.j0 = b.j0, c.nx = b.nx, c.ny = b.ny, c.pitch = b.pitch;
+    c.rank = b.rank, c.nranks = nranks();
+    c.w = array(l, 0), c.r = array(l, 1), c.p[0] = array(l, 2), c.p[1] = array(l, 3);
+    c.Ap = array(l, 4), c.a = array(l, 5), c.b = array(l, 6), c.D = array(l, 7);
+    for (int d = 0; d < 4; ++d) {
+      c.nbr[d] = b.nbr[d];
+      if (b.nbr[d] >= 0) {
+        const LocalBlock nb = make_local_block(grid_.M, grid_.N, pg_, b.nbr[d]);
+        c.nbr_r[d] = reinterpret_cast<double*>(static_cast<char*>(peer_base_[b.nbr[d]]) + kHeaderBytes);
+        c.nbr_pitch[d] = nb.pitch, c.nbr_nx[d] = nb.nx, c.nbr_ny[d] = nb.ny;
+      }
+    }
+    c.partials = reinterpret_cast<double*>(arenas_[l] + kPartialsOffset);
+    c.arrive = reinterpret_cast<unsigned int*>(arenas_[l] + kArriveOffset);
+    c.slots = reinterpret_cast<unsigned long long*>(arenas_[l] + kSlotsOffset);
+    for (int rk = 0; rk < nranks(); ++rk)
+      c.peer_slots[rk] = reinterpret_cast<unsigned long long*>(static_cast<char*>(peer_base_[rk]) + kSlotsOffset);
+    c.ctl = control(l);
+    c.tiles_x = (b.nx + kTileX - 1) / kTileX;
+    c.tiles_y = (b.ny + kTileY - 1) / kTileY;
+    hctx_.push_back(c);
+  }
+  PB_CUDA_CHECK(cudaMemcpy(dctx_, hctx_.data(), sizeof(RankCtx) * nlocal(), cudaMemcpyHostToDevice));
+  finalized_ = true;
+}
+
+}  // namespace pb

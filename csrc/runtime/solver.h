@@ -1,0 +1,96 @@
+// solver.h -- host-side driver of the GPU solver: owns the arenas of the local ranks, knows the peers,
+// builds the device contexts and runs a solve.
+//
+// Replaces gradient_solver_mpi's host part (S4:687-982): allocation (S4:737-768), the iteration loop
+// (now one cooperative launch), the timer collection (S4:955-979).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/poisson_b200.h"
+#include "../cuda/ctx.h"
+
+namespace pb {
+
+enum Method : int { kMethodPersistent = 0, kMethodStepFused = 1, kMethodStepClassic = 2 };
+
+struct SolveOptions {
+  int method = kMethodPersistent;
+  int norm = PB_NORM_WEIGHTED;
+  double delta = 1e-6;
+  long long max_iter = -1;  // <0: (M-1)(N-1)
+  int exact_div = 1;        // literal fp64 divisions (reference association)
+  int ctas_per_sm = 0;      // 0 = auto
+  int error_report = 1;
+  double watchdog_s = 0.0;  // 0 = default (20 s)
+};
+
+// Options as they travel host -> device every solve (pinned staging buffer -> Control).
+struct DeviceOptions {
+  double delta;
+  long long max_iter;
+  int norm;
+  int pad;
+  unsigned long long watchdog_ns;
+};
+
+class Solver {
+ public:
+  Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int device);
+  ~Solver();
+  Solver(const Solver&) = delete;
+  Solver& operator=(const Solver&) = delete;
+
+  int nlocal() const { return (int)blocks_.size(); }
+  int nranks() const { return pg_.Px * pg_.Py; }
+  int first_rank() const { return first_rank_; }
+  int device() const { return device_; }
+  const LocalBlock& block(int l) const { return blocks_[l]; }
+  const RankCtx& host_ctx(int l) const { return hctx_[l]; }
+  const RankCtx* device_ctx(int l) const { return dctx_ + l; }
+  char* arena(int l) const { return arenas_[l]; }
+  size_t arena_size(int l) const { return arena_bytes(blocks_[l]); }
+  double* array(int l, int which) const;  // 0 w, 1 r, 2 p0, 3 p1, 4 Ap, 5 a, 6 b, 7 D
+  Control* control(int l) const { return reinterpret_cast<Control*>(arenas_[l] + kCtlOffset); }
+
+  void ipc_handle(int l, void* out64) const;
+  void open_peer(int rank, const void* handle64);
+  void set_peer_base(int rank, void* base);
+  void finalize();  // all peers known -> build and upload the contexts
+
+  void solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out);
+  // dense (M+1) x (N+1) host field from the local ranks' blocks (other ranks' nodes are left untouched)
+  void copy_solution_to_host(double* full, cudaStream_t stream);
+  // dense nx x ny device copy of one local block's owned nodes
+  void gather_block(int l, double* dev_out, long long ld, cudaStream_t stream);
+
+  int last_ctas_per_rank() const { return last_ctas_per_rank_; }
+  long long last_launches() const { return last_launches_; }
+  size_t h2d_bytes_per_solve() const { return sizeof(DeviceOptions) * blocks_.size(); }
+  size_t d2h_bytes_per_solve() const { return sizeof(Control) * blocks_.size(); }
+
+ private:
+  void solve_persistent(const SolveOptions& opt, cudaStream_t stream);
+  void solve_steps(const SolveOptions& opt, cudaStream_t stream);
+
+  Grid grid_;
+  ProcGrid pg_;
+  int first_rank_, device_;
+  bool finalized_ = false;
+  std::vector<LocalBlock> blocks_;
+  std::vector<char*> arenas_;
+  std::vector<void*> peer_base_;     // per global rank: arena base as seen from this device
+  std::vector<void*> opened_ipc_;    // bases obtained from cudaIpcOpenMemHandle (to close)
+  std::vector<RankCtx> hctx_;
+  RankCtx* dctx_ = nullptr;
+  DeviceOptions* pinned_opts_ = nullptr;
+  Control* pinned_ctl_ = nullptr;
+  cudaEvent_t ev_[4];
+  int sm_count_ = 148;
+  int last_ctas_per_rank_ = 0;
+  long long last_launches_ = 0;
+};
+
+}  // namespace pb

@@ -1,0 +1,158 @@
+// solver_run.cu -- Solver::solve and friends (the part of solver.h that enqueues work).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "../api/error.h"
+#include "../cuda/launch.h"
+#include "solver.h"
+
+namespace pb {
+
+void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
+  const bool exact = opt.exact_div != 0;
+  int per_sm = persistent_max_ctas_per_sm(exact);
+  if (per_sm < 1) throw std::runtime_error("persistent kernel does not fit on an SM");
+  if (opt.ctas_per_sm > 0) per_sm = std::min(per_sm, opt.ctas_per_sm);
+  int max_tiles = 1;
+  for (const RankCtx& c : hctx_) max_tiles = std::max(max_tiles, c.tiles_x * c.tiles_y);
+  int ctas = (per_sm * sm_count_) / nlocal();
+  ctas = std::min(ctas, kMaxCtas);
+  ctas = std::min(ctas, max_tiles);
+  if (ctas < 1) throw std::runtime_error("too many virtual ranks for one cooperative launch");
+  last_ctas_per_rank_ = ctas;
+  for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
+  PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
+  last_launches_ += 1;
+}
+
+// Separate launches per phase; only for a solver whose ranks are all local and alone (nranks == 1):
+// distributed step-wise runs are driven from Python with a library collective between the launches.
+void Solver::solve_steps(const SolveOptions& opt, cudaStream_t stream) {
+  if (nranks() != 1) throw std::runtime_error("step-wise solve from C++ supports a single rank only");
+  const bool fused = opt.method == kMethodStepFused, exact = opt.exact_div != 0;
+  const RankCtx& h = hctx_[0];
+  const RankCtx* d = dctx_;
+  const long long max_iter = pinned_opts_->max_iter;
+  PB_CUDA_CHECK(launch_step_begin(d, stream));
+  PB_CUDA_CHECK(launch_step_dot_zr(d, h, stream));
+  PB_CUDA_CHECK(launch_step_reduce_local(d, h, 1, stream));
+  PB_CUDA_CHECK(launch_step_scalars(d, kStepInit, stream));
+  last_launches_ += 4;
+  const int chunk = 64;
+  int* pinned_status = reinterpret_cast<int*>(pinned_ctl_);  // reused as a 4-byte mailbox here
+  for (long long k = 0; k < max_iter; k += chunk) {
+    const long long n = std::min<long long>(chunk, max_iter - k);
+    for (long long i = 0; i < n; ++i) {
+      if (!fused) {  // p = r/D + beta p (beta = 0, p = 0 in the first iteration)
+        PB_CUDA_CHECK(launch_step_update_p(d, h, stream));
+        last_launches_ += 1;
+      }
+      PB_CUDA_CHECK(launch_step_stencil(d, h, fused, exact, stream));
+      PB_CUDA_CHECK(launch_step_reduce_local(d, h, 1, stream));
+      PB_CUDA_CHECK(launch_step_scalars(d, kStepAlpha, stream));
+      PB_CUDA_CHECK(launch_step_update(d, h, fused, stream));
+      PB_CUDA_CHECK(launch_step_reduce_local(d, h, 2, stream));
+      PB_CUDA_CHECK(launch_step_scalars(d, kStepBeta, stream));
+      last_launches_ += fused ? 7 : 6;
+    }
+    PB_CUDA_CHECK(cudaMemcpyAsync(pinned_status, &control(0)->status, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    PB_CUDA_CHECK(cudaStreamSynchronize(stream));
+    if (*pinned_status != PB_STATUS_RUNNING) break;
+  }
+}
+
+void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) {
+  if (!finalized_) throw std::runtime_error("Solver::solve before finalize()");
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  last_launches_ = 0;
+  // 1. options: pinned host -> device (the only input of a solve besides M, N fixed at creation)
+  pinned_opts_->delta = opt.delta;
+  pinned_opts_->max_iter = opt.max_iter >= 0 ? opt.max_iter : (long long)(grid_.M - 1) * (long long)(grid_.N - 1);
+  pinned_opts_->norm = opt.norm;
+  pinned_opts_->pad = 0;
+  pinned_opts_->watchdog_ns = opt.watchdog_s > 0.0 ? (unsigned long long)(opt.watchdog_s * 1e9) : 0ull;
+  for (int l = 0; l < nlocal(); ++l)
+    PB_CUDA_CHECK(cudaMemcpyAsync(&control(l)->delta, pinned_opts_, sizeof(DeviceOptions), cudaMemcpyHostToDevice,
+                                  stream));
+  // 2. assembly, iteration, error report -- all enqueued, no host synchronisation in between
+  PB_CUDA_CHECK(cudaEventRecord(ev_[0], stream));
+  for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(launch_assemble(dctx_ + l, hctx_[l], stream));
+  last_launches_ += nlocal();
+  PB_CUDA_CHECK(cudaEventRecord(ev_[1], stream));
+  if (opt.method == kMethodPersistent)
+    solve_persistent(opt, stream);
+  else
+    solve_steps(opt, stream);
+  PB_CUDA_CHECK(cudaEventRecord(ev_[2], stream));
+  if (opt.error_report) {
+    for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(launch_error_report(dctx_ + l, hctx_[l], stream));
+    last_launches_ += nlocal();
+  }
+  PB_CUDA_CHECK(cudaEventRecord(ev_[3], stream));
+  // 3. results: device -> pinned host
+  for (int l = 0; l < nlocal(); ++l)
+    PB_CUDA_CHECK(cudaMemcpyAsync(pinned_ctl_ + l, control(l), sizeof(Control), cudaMemcpyDeviceToHost, stream));
+  PB_CUDA_CHECK(cudaStreamSynchronize(stream));
+
+  if (!out) return;
+  std::memset(out, 0, sizeof(*out));
+  float ms_asm = 0, ms_iter = 0, ms_err = 0;
+  PB_CUDA_CHECK(cudaEventElapsedTime(&ms_asm, ev_[0], ev_[1]));
+  PB_CUDA_CHECK(cudaEventElapsedTime(&ms_iter, ev_[1], ev_[2]));
+  PB_CUDA_CHECK(cudaEventElapsedTime(&ms_err, ev_[2], ev_[3]));
+  const Control& c0 = pinned_ctl_[0];
+  out->iters = c0.iter;
+  out->status = c0.status;
+  out->diff_norm = c0.diff_norm;
+  double s_in = 0, s_all = 0, mx = 0, mw = -1e300, cnt = 0;
+  unsigned long long t_ab = 0, t_c = 0, t_r1 = 0, t_r2 = 0, t_init = 0;
+  for (int l = 0; l < nlocal(); ++l) {
+    const Control& c = pinned_ctl_[l];
+    if (c.status == PB_STATUS_WATCHDOG) out->status = PB_STATUS_WATCHDOG;
+    s_in += c.err[0], s_all += c.err[1], cnt += c.err[4];
+    mx = std::max(mx, c.err[2]), mw = std::max(mw, c.err[3]);
+    t_ab = std::max(t_ab, c.t_ab), t_c = std::max(t_c, c.t_c), t_r1 = std::max(t_r1, c.t_red1);
+    t_r2 = std::max(t_r2, c.t_red2), t_init = std::max(t_init, c.t_init);
+  }
+  out->sum_e2_in_D = s_in;
+  out->sum_e2_all = s_all;
+  out->l2_in_D = std::sqrt(grid_.h1h2 * s_in);
+  out->l2_all = std::sqrt(grid_.h1h2 * s_all);
+  out->max_abs = mx;
+  out->max_w = mw;
+  out->nodes_in_D = (long long)cnt;
+  out->seconds = 1e-3 * (double)(ms_asm + ms_iter + ms_err);
+  out->t_assemble = 1e-3 * ms_asm;
+  out->t_iterations = 1e-3 * ms_iter;
+  if (opt.method == kMethodPersistent) {
+    out->t_gpu = 1e-9 * (double)(t_ab + t_c);
+    out->t_dot = 1e-9 * (double)(t_r1 + t_r2 + t_init);
+    out->t_comm = nranks() > 1 ? 1e-9 * (double)(t_r1 + t_r2) : 0.0;
+    out->t_precond = 0.25 * 1e-9 * (double)t_c;  // attributed share of phase C (one of its four streams)
+  } else {
+    out->t_gpu = 1e-3 * ms_iter;
+  }
+  out->t_copy = 0.0;
+}
+
+void Solver::gather_block(int l, double* dev_out, long long ld, cudaStream_t stream) {
+  const LocalBlock& b = blocks_[l];
+  PB_CUDA_CHECK(launch_gather_interior(array(l, 0), b.nx, b.ny, b.pitch, dev_out, ld, stream));
+}
+
+void Solver::copy_solution_to_host(double* full, cudaStream_t stream) {
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  const int S = grid_.N + 1;
+  for (int l = 0; l < nlocal(); ++l) {
+    const LocalBlock& b = blocks_[l];
+    // strided D2H: rows li = 1..nx, columns lj = 1..ny of w -> full[(i0 + li - 1) * S + j0 + lj - 1]
+    PB_CUDA_CHECK(cudaMemcpy2DAsync(full + (size_t)b.i0 * S + b.j0, sizeof(double) * S,
+                                    array(l, 0) + b.index(1, 1), sizeof(double) * b.pitch, sizeof(double) * b.ny,
+                                    b.nx, cudaMemcpyDeviceToHost, stream));
+  }
+  PB_CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+
+}  // namespace pb

@@ -1,0 +1,154 @@
+/* poisson_b200.h -- C ABI of libpoisson_b200.
+ *
+ * Everything the Python package, the CLI and third-party callers use goes through these functions.
+ * All functions return 0 on success and a negative value on failure unless stated otherwise;
+ * pb_last_error() gives the message of the last failure on the calling thread.
+ *
+ * Reference parity tags (SURVEY.md legend): S0..S4 are the stage sources of
+ * mxy-kit/poisson-ellipse-openmp-mpi-cuda; each declaration names what it replaces.
+ */
+#ifndef POISSON_B200_H
+#define POISSON_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB_NORM_WEIGHTED 0   /* sqrt(h1 h2 sum dw^2)  -- stages 1-4 (S4:656-659, S4:896) */
+#define PB_NORM_UNWEIGHTED 1 /* sqrt(sum dw^2)        -- stage 0   (S0:149-154)         */
+
+#define PB_STATUS_MAXITER 0
+#define PB_STATUS_CONVERGED 1
+#define PB_STATUS_BREAKDOWN 2 /* |(Ap,p)| < 1e-15 (S4:875) */
+#define PB_STATUS_RUNNING 3
+#define PB_STATUS_WATCHDOG 4 /* a device-side wait timed out; the solve was abandoned */
+
+/* Result of a solve.  Timers are seconds; for multi-rank runs the caller takes the max over ranks. */
+typedef struct pb_stats {
+  int iters;
+  int status;
+  double diff_norm;  /* last ||w(k+1)-w(k)|| in the selected norm */
+  double l2_in_D;    /* sqrt(h1 h2 sum_{nodes in D} (w-u)^2) */
+  double l2_all;     /* same over all interior nodes (u = 0 outside D) */
+  double max_abs;    /* max |w-u| */
+  double max_w;      /* max w */
+  long long nodes_in_D;
+  double seconds;    /* solver time: assembly + iterations (+ error report), device-timed on GPU */
+  /* the reference's five buckets (S4:695-700), fed from device-side clocks on the GPU paths */
+  double t_gpu;      /* stencil + update phases */
+  double t_copy;     /* host<->device copies inside the solve (0 on the fused paths) */
+  double t_comm;     /* waiting for halo data / cross-GPU reductions */
+  double t_precond;  /* share of t_gpu spent in z = r/D (attributed) */
+  double t_dot;      /* reduction phases */
+  double t_assemble; /* coefficient / right-hand-side assembly */
+  double t_iterations; /* the PCG loop alone (CUDA events) */
+  double sum_e2_in_D; /* raw sums of squared errors over the local ranks, for cross-process reduction */
+  double sum_e2_all;
+} pb_stats;
+
+/* Local block of the 2-D decomposition in the padded layout (see csrc/core/decomp.h). */
+typedef struct pb_block {
+  int rank, px, py;
+  int i0, j0; /* global indices of local (1,1) */
+  int nx, ny; /* owned nodes */
+  int pitch;  /* doubles per row */
+  int nbr[4]; /* x-, x+, y-, y+ neighbour ranks or -1 */
+} pb_block;
+
+int pb_version(void);
+const char* pb_last_error(void);
+
+/* ---- decomposition (replaces choose_process_grid S4:82-86 and decompose_2d S4:97-133) ---- */
+void pb_choose_proc_grid(int nranks, int* Px, int* Py);
+int pb_local_block(int M, int N, int Px, int Py, int rank, pb_block* out);
+int pb_col_offset(void); /* column of ring cell lj=0 inside a padded row */
+
+/* ---- scalar problem definition (replaces S4:32-76, S4:162-191) ---- */
+double pb_coef_a(int M, int N, int i, int j);
+double pb_coef_b(int M, int N, int i, int j);
+double pb_rhs(int M, int N, int i, int j);
+double pb_diag(int M, int N, int i, int j);
+double pb_chord(double fixed, double lo, double hi, int vertical);
+double pb_exact(double x, double y);
+
+/* ---- CPU solver: oracle and CPU baseline (replaces stages 0/1: S0:106-172, S1:133-199) ---- */
+int pb_cpu_solve(int M, int N, int norm, double delta, long long max_iter, int threads,
+                 int signed_breakdown, double* w_out /* (M+1)*(N+1) or NULL */, pb_stats* stats);
+int pb_cpu_error_report(int M, int N, const double* w, pb_stats* stats);
+
+/* ---- CPU local-block operations for the distributed CPU backend (replaces the per-rank loops of
+ *      stages 2/3: S2:124-232, S2:418-456) ---- */
+int pb_cpu_assemble_local(int M, int N, const pb_block* blk, double* a, double* b, double* D, double* rhs,
+                          int threads);
+double pb_cpu_apply_A_local(int M, int N, const pb_block* blk, const double* p, const double* a,
+                            const double* b, double* Ap, int threads);
+int pb_cpu_update_wr_local(const pb_block* blk, double* w, double* r, const double* p, const double* Ap,
+                           const double* D, double alpha, double* out2, int threads);
+int pb_cpu_update_p_local(const pb_block* blk, double* p, const double* r, const double* D, double beta,
+                          int threads);
+double pb_cpu_dot_zr_local(const pb_block* blk, const double* r, const double* D, int threads);
+int pb_cpu_error_local(int M, int N, const pb_block* blk, const double* w, double* out5);
+
+/* ---- GPU solver (replaces gradient_solver_mpi S4:687-982 and its kernels S4:507-676) ----
+ * A pb_solver owns the device memory ("arena") of `nlocal` consecutive ranks of a Px x Py process grid on
+ * one device.  Multi-GPU: one process per GPU creates a solver with nlocal = 1, exchanges the 64-byte IPC
+ * handles with its peers (pb_solver_ipc_handle / pb_solver_open_peer), then calls pb_solver_finalize.
+ * Single-GPU "virtual ranks": nlocal = Px*Py, no exchange needed. */
+typedef struct pb_solver pb_solver;
+
+#define PB_METHOD_PERSISTENT 0   /* one cooperative launch per solve, fused halo + reductions */
+#define PB_METHOD_STEP_FUSED 1   /* separate launches, fused p-update + stencil (single rank) */
+#define PB_METHOD_STEP_CLASSIC 2 /* separate launches, reference-like 3-kernel structure (single rank) */
+
+typedef struct pb_solve_options {
+  int method;
+  int norm;
+  double delta;
+  long long max_iter; /* < 0: (M-1)(N-1) as in S4:1006 */
+  int exact_div;      /* 1: literal fp64 divisions; 0: reciprocal multiplications in the stencil */
+  int ctas_per_sm;    /* 0 = auto */
+  int error_report;   /* 1: compute the error against the analytic solution after the solve */
+  int pad;
+  double watchdog_s;  /* 0 = default (20 s): device-side waits give up after this long */
+} pb_solve_options;
+
+int pb_cuda_device_count(void);
+pb_solver* pb_solver_create(int M, int N, int Px, int Py, int first_rank, int nlocal, int device);
+void pb_solver_destroy(pb_solver* s);
+int pb_solver_ipc_handle(pb_solver* s, int local_idx, void* out64);
+int pb_solver_open_peer(pb_solver* s, int rank, const void* handle64);
+int pb_solver_set_peer_base(pb_solver* s, int rank, void* arena_base);
+void* pb_solver_arena(pb_solver* s, int local_idx);
+int pb_solver_finalize(pb_solver* s);
+int pb_solver_solve(pb_solver* s, const pb_solve_options* opt, void* cuda_stream, pb_stats* stats);
+int pb_solver_block(pb_solver* s, int local_idx, pb_block* out);
+/* device pointer of a local array: 0 w, 1 r, 2 p0, 3 p1, 4 Ap, 5 a, 6 b, 7 D; (nx+2) x pitch doubles */
+void* pb_solver_array(pb_solver* s, int local_idx, int which);
+void* pb_solver_control_red(pb_solver* s, int local_idx); /* device double[4]: staging of step reductions */
+void* pb_solver_control_err(pb_solver* s, int local_idx); /* device double[5]: error report partials */
+int pb_solver_copy_solution(pb_solver* s, double* host_full /* (M+1)*(N+1) */, void* cuda_stream);
+int pb_solver_gather_block(pb_solver* s, int local_idx, void* dev_out, long long ld, void* cuda_stream);
+int pb_solver_info(pb_solver* s, int* ctas_per_rank, long long* launches, long long* h2d_bytes, long long* d2h_bytes);
+
+/* kernel-level step API (library-collective baseline: the caller runs NCCL / gloo between the launches) */
+int pb_step_set_options(pb_solver* s, int norm, double delta, long long max_iter, void* cuda_stream);
+int pb_step_assemble(pb_solver* s, int local_idx, void* cuda_stream);
+int pb_step_begin(pb_solver* s, int local_idx, void* cuda_stream);
+int pb_step_dot_zr(pb_solver* s, int local_idx, void* cuda_stream);
+int pb_step_stencil(pb_solver* s, int local_idx, int fuse_p, int exact_div, void* cuda_stream);
+int pb_step_update(pb_solver* s, int local_idx, int fuse_p, void* cuda_stream);
+int pb_step_update_p(pb_solver* s, int local_idx, void* cuda_stream);
+int pb_step_reduce_local(pb_solver* s, int local_idx, int nvalues, void* cuda_stream);
+int pb_step_scalars(pb_solver* s, int local_idx, int phase /* 0 init, 1 alpha, 2 beta */, void* cuda_stream);
+int pb_step_pack_edges(pb_solver* s, int local_idx, void* dev_buf, int stride, void* cuda_stream);
+int pb_step_unpack_edges(pb_solver* s, int local_idx, const void* dev_buf, int stride, void* cuda_stream);
+int pb_step_error_report(pb_solver* s, int local_idx, void* cuda_stream);
+int pb_step_read_control(pb_solver* s, int local_idx, int* iter, int* status, double* diff_norm, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POISSON_B200_H */

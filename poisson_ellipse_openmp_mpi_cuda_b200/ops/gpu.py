@@ -1,0 +1,176 @@
+"""GPU solver objects: a thin, typed wrapper around ``pb_solver`` (C ABI) that hands out torch views.
+
+The device arrays are owned by the native arena (one ``cudaMalloc`` per rank, exportable through CUDA
+IPC); torch tensors returned here alias that memory through ``__cuda_array_interface__``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from . import _native
+
+NORMS = {"weighted": 0, "unweighted": 1}
+METHODS = {"persistent": 0, "step_fused": 1, "step_classic": 2}
+STATUS = {0: "max_iter", 1: "converged", 2: "breakdown", 3: "running", 4: "watchdog"}
+ARRAYS = {"w": 0, "r": 1, "p0": 2, "p1": 3, "Ap": 4, "a": 5, "b": 6, "D": 7}
+
+
+class _DevMem:
+    """Minimal ``__cuda_array_interface__`` carrier for memory owned by the native library."""
+
+    def __init__(self, ptr: int, shape, typestr: str, owner):
+        self.__cuda_array_interface__ = {
+            "shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3, "strides": None,
+        }
+        self._owner = owner  # keeps the solver alive while views exist
+
+
+def _stream_ptr(stream) -> int:
+    if stream is None:
+        stream = torch.cuda.current_stream()
+    return int(stream.cuda_stream)
+
+
+@dataclass
+class BlockInfo:
+    rank: int
+    px: int
+    py: int
+    i0: int
+    j0: int
+    nx: int
+    ny: int
+    pitch: int
+    nbr: tuple
+
+
+class GpuSolver:
+    """Owns the arenas of ``nlocal`` consecutive ranks of a ``Px x Py`` grid on one device."""
+
+    def __init__(self, M: int, N: int, Px: int = 1, Py: int = 1, first_rank: int = 0, nlocal: int | None = None,
+                 device: int | None = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("GpuSolver needs a CUDA device (torch.cuda.is_available() is False)")
+        self.lib = _native.lib()
+        self.M, self.N, self.Px, self.Py = M, N, Px, Py
+        self.first_rank = first_rank
+        self.nlocal = Px * Py if nlocal is None else nlocal
+        self.device = torch.cuda.current_device() if device is None else device
+        torch.cuda.init()
+        self._h = self.lib.pb_solver_create(M, N, Px, Py, first_rank, self.nlocal, self.device)
+        if not self._h:
+            raise RuntimeError(f"pb_solver_create failed: {_native.last_error()}")
+        self._finalized = False
+        self.col_off = self.lib.pb_col_offset()
+
+    # -- lifetime -------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.pb_solver_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- peers ----------------------------------------------------------------------------------
+    def ipc_handle(self, local_idx: int = 0) -> bytes:
+        buf = C.create_string_buffer(64)
+        _native.check(self.lib.pb_solver_ipc_handle(self._h, local_idx, buf), "pb_solver_ipc_handle")
+        return buf.raw
+
+    def open_peer(self, rank: int, handle: bytes):
+        _native.check(self.lib.pb_solver_open_peer(self._h, rank, C.create_string_buffer(handle, 64)),
+                      "pb_solver_open_peer")
+
+    def finalize(self):
+        _native.check(self.lib.pb_solver_finalize(self._h), "pb_solver_finalize")
+        self._finalized = True
+        return self
+
+    # -- info -----------------------------------------------------------------------------------
+    def block(self, local_idx: int = 0) -> BlockInfo:
+        b = _native.Block()
+        _native.check(self.lib.pb_solver_block(self._h, local_idx, C.byref(b)), "pb_solver_block")
+        return BlockInfo(b.rank, b.px, b.py, b.i0, b.j0, b.nx, b.ny, b.pitch, tuple(b.nbr))
+
+    def array(self, name: str, local_idx: int = 0) -> torch.Tensor:
+        """Padded ``(nx+2, pitch)`` float64 view of a device array (ring at row/col 0 and nx+1/ny+1;
+        column ``lj`` lives at ``lj + col_off``)."""
+        blk = self.block(local_idx)
+        ptr = self.lib.pb_solver_array(self._h, local_idx, ARRAYS[name])
+        if not ptr:
+            raise RuntimeError(_native.last_error())
+        return torch.as_tensor(_DevMem(ptr, (blk.nx + 2, blk.pitch), "<f8", self), device=f"cuda:{self.device}")
+
+    def interior(self, name: str, local_idx: int = 0) -> torch.Tensor:
+        blk = self.block(local_idx)
+        return self.array(name, local_idx)[1:blk.nx + 1, self.col_off + 1:self.col_off + 1 + blk.ny]
+
+    def control_red(self, local_idx: int = 0) -> torch.Tensor:
+        ptr = self.lib.pb_solver_control_red(self._h, local_idx)
+        return torch.as_tensor(_DevMem(ptr, (4,), "<f8", self), device=f"cuda:{self.device}")
+
+    def control_err(self, local_idx: int = 0) -> torch.Tensor:
+        ptr = self.lib.pb_solver_control_err(self._h, local_idx)
+        return torch.as_tensor(_DevMem(ptr, (5,), "<f8", self), device=f"cuda:{self.device}")
+
+    def info(self) -> dict:
+        ctas, launches, h2d, d2h = C.c_int(), C.c_longlong(), C.c_longlong(), C.c_longlong()
+        self.lib.pb_solver_info(self._h, C.byref(ctas), C.byref(launches), C.byref(h2d), C.byref(d2h))
+        return {"ctas_per_rank": ctas.value, "launches": launches.value, "h2d_bytes": h2d.value,
+                "d2h_bytes": d2h.value}
+
+    # -- solve ----------------------------------------------------------------------------------
+    def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
+              exact_div: bool = True, ctas_per_sm: int = 0, error_report: bool = True, watchdog_s: float = 0.0,
+              stream=None) -> dict:
+        if not self._finalized:
+            self.finalize()
+        opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, int(exact_div), ctas_per_sm,
+                                   int(error_report), 0, watchdog_s)
+        st = _native.Stats()
+        with torch.cuda.device(self.device):
+            _native.check(self.lib.pb_solver_solve(self._h, C.byref(opt), _stream_ptr(stream), C.byref(st)),
+                          "pb_solver_solve")
+        out = st.as_dict()
+        out["status_name"] = STATUS.get(st.status, "?")
+        out.update(self.info())
+        if st.status == 4:
+            raise RuntimeError("device-side watchdog fired: a rank did not reach a reduction in time")
+        return out
+
+    def solution_host(self) -> torch.Tensor:
+        """Dense ``(M+1, N+1)`` host field; only nodes owned by local ranks are filled."""
+        full = torch.zeros((self.M + 1, self.N + 1), dtype=torch.float64).pin_memory()
+        _native.check(self.lib.pb_solver_copy_solution(self._h, full.data_ptr(), _stream_ptr(None)),
+                      "pb_solver_copy_solution")
+        return full
+
+    def gather_block(self, local_idx: int = 0) -> torch.Tensor:
+        """Dense ``(nx, ny)`` device copy of the owned nodes of ``w`` (native gather kernel)."""
+        blk = self.block(local_idx)
+        out = torch.empty((blk.nx, blk.ny), dtype=torch.float64, device=f"cuda:{self.device}")
+        _native.check(self.lib.pb_solver_gather_block(self._h, local_idx, out.data_ptr(), blk.ny, _stream_ptr(None)),
+                      "pb_solver_gather_block")
+        return out
+
+    # -- kernel-level step API ------------------------------------------------------------------
+    def step(self, name: str, *args, local_idx: int = 0, stream=None):
+        fn = getattr(self.lib, f"pb_step_{name}")
+        if name == "set_options":
+            rc = fn(self._h, *args, _stream_ptr(stream))
+        else:
+            rc = fn(self._h, local_idx, *args, _stream_ptr(stream))
+        _native.check(rc, f"pb_step_{name}")
+
+    def read_control(self, local_idx: int = 0) -> dict:
+        it, stt, dn = C.c_int(), C.c_int(), C.c_double()
+        _native.check(self.lib.pb_step_read_control(self._h, local_idx, C.byref(it), C.byref(stt), C.byref(dn),
+                                                    _stream_ptr(None)), "pb_step_read_control")
+        return {"iters": it.value, "status": stt.value, "diff_norm": dn.value}
