@@ -98,7 +98,7 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
 #pragma unroll
     for (int k = 0; k < NV; ++k) c.partials[cta * kPartialStride + k] = val[k];
     // release: partials (and any halo values this CTA stored into a neighbour GPU) before the arrival
-    if (did_peer_stores)
+    if (did_peer_stores && c.sys_scope)
       fence_acq_rel_sys();
     else
       fence_acq_rel_gpu();
@@ -108,7 +108,7 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
   __syncthreads();
   if (s_last) {
     // aggregator: acquire everyone's partials, sum them in a fixed tree, publish to all ranks
-    if (threadIdx.x == 0) fence_acq_rel_sys();
+    if (threadIdx.x == 0) fence_acq_rel_gpu();
     __syncthreads();
     double acc[NV];
 #pragma unroll
@@ -134,7 +134,10 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
       }
       const size_t off = ((size_t)(seq & 1u) * kMaxRanks + (size_t)c.rank) * kSlotWords;
       unsigned long long* dst = c.peer_slots[threadIdx.x] + off;
-      fence_acq_rel_sys();  // release (cumulative over the halo stores acquired through the arrivals)
+      if (c.sys_scope)
+        fence_acq_rel_sys();  // release (cumulative over the halo stores acquired through the arrivals)
+      else
+        fence_acq_rel_gpu();
 #pragma unroll
       for (int q = 0; q < kSlotWords; ++q) st_relaxed_sys_u64(dst + q, words[q]);
     }
@@ -178,7 +181,10 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
         mine[k] = __longlong_as_double((long long)bits);
       }
     }
-    fence_acq_rel_sys();  // acquire: halo values stored by neighbours before their arrival
+    if (c.sys_scope)
+      fence_acq_rel_sys();  // acquire: halo values stored by neighbours before their arrival
+    else
+      fence_acq_rel_gpu();
     ok = __all_sync(0xffffffffu, ok);
     // rank-ordered sum, identical everywhere
     double tot[kRedValues];

@@ -22,7 +22,7 @@
 namespace pb {
 
 template <bool EXACT>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
   __shared__ RankCtx c;
   __shared__ double s_red[80];

@@ -89,8 +89,11 @@ void Solver::set_peer_base(int rank, void* base) {
 
 void Solver::finalize() {
   PB_CUDA_CHECK(cudaSetDevice(device_));
+  // Ranks whose arena is unknown are unreachable: no halo stores, no in-kernel reductions (the
+  // library-collective baseline runs like this); the persistent method then refuses to start.
+  fabric_complete_ = true;
   for (int rk = 0; rk < nranks(); ++rk)
-    if (!peer_base_[rk]) throw std::runtime_error("Solver::finalize: arena of rank " + std::to_string(rk) + " unknown");
+    if (!peer_base_[rk]) fabric_complete_ = false;
   hctx_.clear();
   for (int l = 0; l < nlocal(); ++l) {
     const LocalBlock& b = blocks_[l];
@@ -103,7 +106,7 @@ void Solver::finalize() {
     c.Ap = array(l, 4), c.a = array(l, 5), c.b = array(l, 6), c.D = array(l, 7);
     for (int d = 0; d < 4; ++d) {
       c.nbr[d] = b.nbr[d];
-      if (b.nbr[d] >= 0) {
+      if (b.nbr[d] >= 0 && peer_base_[b.nbr[d]]) {
         const LocalBlock nb = make_local_block(grid_.M, grid_.N, pg_, b.nbr[d]);
         c.nbr_r[d] = reinterpret_cast<double*>(static_cast<char*>(peer_base_[b.nbr[d]]) + kHeaderBytes);
         c.nbr_pitch[d] = nb.pitch, c.nbr_nx[d] = nb.nx, c.nbr_ny[d] = nb.ny;
@@ -113,8 +116,10 @@ void Solver::finalize() {
     c.arrive = reinterpret_cast<unsigned int*>(arenas_[l] + kArriveOffset);
     c.slots = reinterpret_cast<unsigned long long*>(arenas_[l] + kSlotsOffset);
     for (int rk = 0; rk < nranks(); ++rk)
-      c.peer_slots[rk] = reinterpret_cast<unsigned long long*>(static_cast<char*>(peer_base_[rk]) + kSlotsOffset);
+      if (peer_base_[rk])
+        c.peer_slots[rk] = reinterpret_cast<unsigned long long*>(static_cast<char*>(peer_base_[rk]) + kSlotsOffset);
     c.ctl = control(l);
+    c.sys_scope = nlocal() != nranks() ? 1 : 0;
     c.tiles_x = (b.nx + kTileX - 1) / kTileX;
     c.tiles_y = (b.ny + kTileY - 1) / kTileY;
     hctx_.push_back(c);

@@ -79,6 +79,7 @@ class Solver {
   ProcGrid pg_;
   int first_rank_, device_;
   bool finalized_ = false;
+  bool fabric_complete_ = false;
   std::vector<LocalBlock> blocks_;
   std::vector<char*> arenas_;
   std::vector<void*> peer_base_;     // per global rank: arena base as seen from this device

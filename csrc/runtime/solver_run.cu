@@ -11,6 +11,7 @@
 namespace pb {
 
 void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
+  if (!fabric_complete_) throw std::runtime_error("persistent solve needs every rank's arena (open_peer) first");
   const bool exact = opt.exact_div != 0;
   int per_sm = persistent_max_ctas_per_sm(exact);
   if (per_sm < 1) throw std::runtime_error("persistent kernel does not fit on an SM");
