@@ -1,14 +1,29 @@
 // c_api_cuda.cu -- C ABI of the GPU solver (see include/poisson_b200.h).
 #include <exception>
+#include <memory>
+#include <vector>
 
 #include "../../include/poisson_b200.h"
 #include "../cuda/launch.h"
+#include "../runtime/group.h"
 #include "../runtime/solver.h"
 #include "error.h"
 
+// A pb_solver either owns its Solver or borrows one that lives inside a pb_group.
 struct pb_solver {
-  pb::Solver impl;
-  pb_solver(int M, int N, int Px, int Py, int first, int nlocal, int dev) : impl(M, N, Px, Py, first, nlocal, dev) {}
+  std::unique_ptr<pb::Solver> owned;
+  pb::Solver& impl;
+  pb_solver(int M, int N, int Px, int Py, int first, int nlocal, int dev)
+      : owned(new pb::Solver(M, N, Px, Py, first, nlocal, dev)), impl(*owned) {}
+  explicit pb_solver(pb::Solver& borrowed) : impl(borrowed) {}
+};
+
+struct pb_group {
+  pb::DeviceGroup impl;
+  std::vector<std::unique_ptr<pb_solver>> views;
+  pb_group(int M, int N, int Px, int Py, const std::vector<int>& devs) : impl(M, N, Px, Py, devs) {
+    for (int r = 0; r < impl.size(); ++r) views.emplace_back(new pb_solver(impl.solver(r)));
+  }
 };
 
 namespace {
@@ -108,6 +123,37 @@ int pb_solver_info(pb_solver* s, int* ctas, long long* launches, long long* h2d,
   if (h2d) *h2d = (long long)s->impl.h2d_bytes_per_solve();
   if (d2h) *d2h = (long long)s->impl.d2h_bytes_per_solve();
   return 0;
+}
+
+// ---- single-process multi-GPU group ----
+pb_group* pb_group_create(int M, int N, int Px, int Py, const int* devices, int ndevices) {
+  try {
+    return new pb_group(M, N, Px, Py, std::vector<int>(devices, devices + ndevices));
+  } catch (const std::exception& e) {
+    pb::set_last_error(e.what());
+    return nullptr;
+  }
+}
+void pb_group_destroy(pb_group* g) { delete g; }
+int pb_group_solve(pb_group* g, const pb_solve_options* o, pb_stats* stats) {
+  return guarded([&] {
+    pb::SolveOptions opt;
+    opt.method = o->method;
+    opt.norm = o->norm;
+    opt.delta = o->delta;
+    opt.max_iter = o->max_iter;
+    opt.exact_div = o->exact_div;
+    opt.ctas_per_sm = o->ctas_per_sm;
+    opt.error_report = o->error_report;
+    opt.watchdog_s = o->watchdog_s;
+    g->impl.solve(opt, stats);
+  });
+}
+int pb_group_copy_solution(pb_group* g, double* host_full) {
+  return guarded([&] { g->impl.copy_solution_to_host(host_full); });
+}
+pb_solver* pb_group_solver(pb_group* g, int rank) {
+  return rank >= 0 && rank < (int)g->views.size() ? g->views[rank].get() : nullptr;
 }
 
 // ---- kernel-level step API ----

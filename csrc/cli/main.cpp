@@ -1,0 +1,199 @@
+// main.cpp -- command-line driver: `poisson_b200 M N [options]`.
+//
+// Keeps the reference's interface (two positional integers, default 40 40 when fewer than two are given,
+// S4:995-999; delta = 1e-6 and max_iter = (M-1)(N-1), S4:1005-1006) and prints the stage-4 report verbatim
+// (S4:1001-1002, S4:900-902, S4:969-978, S4:1027-1033), followed by the lines the reference lacks (error
+// against the analytic solution, device time per iteration).  `--stage 0|1` selects the CPU programs'
+// behaviour and formats (S0:176-196, S1:204-229).
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "../../include/poisson_b200.h"
+
+namespace {
+
+double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+void usage() {
+  std::cout << "usage: poisson_b200 [M N] [--gpus G] [--grid PxxPy] [--virtual] [--norm weighted|unweighted]\n"
+               "                    [--delta D] [--max-iter K] [--method persistent|step_fused|step_classic]\n"
+               "                    [--fast-div] [--dump FILE] [--stage 0|1|4] [--threads T] [--quiet-extras]\n";
+}
+
+void dump_solution(const std::string& path, const std::vector<double>& w, int M, int N) {
+  const bool bin = path.size() > 4 && path.substr(path.size() - 4) == ".bin";
+  if (bin) {
+    std::ofstream f(path, std::ios::binary);
+    f << "poisson_b200 " << M << " " << N << " float64 little-endian row=i(x) col=j(y)\n";
+    f.write(reinterpret_cast<const char*>(w.data()), (std::streamsize)(w.size() * sizeof(double)));
+    return;
+  }
+  std::ofstream f(path);
+  f << std::setprecision(17);
+  const double h1 = 2.0 / M, h2 = 1.2 / N;
+  for (int i = 0; i <= M; ++i) {
+    for (int j = 0; j <= N; ++j) f << (-1.0 + i * h1) << " " << (-0.6 + j * h2) << " " << w[(size_t)i * (N + 1) + j] << "\n";
+    f << "\n";
+  }
+}
+
+void print_extras(const pb_stats& st) {
+  std::printf("   L2 error vs analytic (in D)  ~ %.9e\n", st.l2_in_D);
+  std::printf("   L2 error vs analytic (all)   ~ %.9e\n", st.l2_all);
+  std::printf("   Max error vs analytic      ~ %.9e\n", st.max_abs);
+  if (st.iters > 0 && st.t_iterations > 0) std::printf("   Device time per iteration    ~ %.3f us\n", 1e6 * st.t_iterations / st.iters);
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  const double t_program_start = now_s();
+  int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4, threads = 1;
+  bool virt = false, extras = true;
+  std::string dump, method = "persistent";
+  pb_solve_options opt{};
+  opt.method = PB_METHOD_PERSISTENT;
+  opt.norm = PB_NORM_WEIGHTED;
+  opt.delta = 1e-6;
+  opt.max_iter = -1;
+  opt.exact_div = 1;
+  opt.error_report = 1;
+  bool norm_set = false;
+
+  std::vector<std::string> pos;
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    auto next = [&]() -> std::string {
+      if (i + 1 >= argc) {
+        usage();
+        std::exit(2);
+      }
+      return argv[++i];
+    };
+    if (a == "--gpus") gpus = std::atoi(next().c_str());
+    else if (a == "--grid") {
+      const std::string g = next();
+      if (std::sscanf(g.c_str(), "%dx%d", &Px, &Py) != 2) { usage(); return 2; }
+    } else if (a == "--virtual") virt = true;
+    else if (a == "--norm") { opt.norm = next() == "unweighted" ? PB_NORM_UNWEIGHTED : PB_NORM_WEIGHTED; norm_set = true; }
+    else if (a == "--delta") opt.delta = std::atof(next().c_str());
+    else if (a == "--max-iter") opt.max_iter = std::atoll(next().c_str());
+    else if (a == "--method") method = next();
+    else if (a == "--fast-div") opt.exact_div = 0;
+    else if (a == "--dump") dump = next();
+    else if (a == "--stage") stage = std::atoi(next().c_str());
+    else if (a == "--threads") threads = std::atoi(next().c_str());
+    else if (a == "--quiet-extras") extras = false;
+    else if (a == "-h" || a == "--help") { usage(); return 0; }
+    else pos.push_back(a);
+  }
+  if (pos.size() >= 2) {  // a single positional argument is ignored, like the reference (argc >= 3)
+    M = std::atoi(pos[0].c_str());
+    N = std::atoi(pos[1].c_str());
+  }
+  if (method == "step_fused") opt.method = PB_METHOD_STEP_FUSED;
+  else if (method == "step_classic") opt.method = PB_METHOD_STEP_CLASSIC;
+
+  // ---- CPU stages ----
+  if (stage == 0 || stage == 1) {
+    if (!norm_set) opt.norm = stage == 0 ? PB_NORM_UNWEIGHTED : PB_NORM_WEIGHTED;
+    std::vector<double> w((size_t)(M + 1) * (N + 1));
+    pb_stats st{};
+    if (pb_cpu_solve(M, N, opt.norm, opt.delta, opt.max_iter, stage == 0 ? 1 : threads, 1, w.data(), &st) != 0) {
+      std::cerr << "error: " << pb_last_error() << "\n";
+      return 1;
+    }
+    if (st.status == PB_STATUS_CONVERGED) {
+      if (stage == 0) std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < δ)." << std::endl;
+      else std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < " << opt.delta << ").\n";
+    }
+    if (stage == 0)
+      std::cout << "M=" << M << ", N=" << N << " | Iter=" << st.iters << " | Time=" << std::fixed << std::setprecision(4)
+                << st.seconds << " s\n";
+    else
+      std::cout << "Threads = " << std::setw(2) << threads << " | Time = " << std::fixed << std::setprecision(3)
+                << st.seconds << " s\n";
+    std::cout.flush();
+    if (extras) print_extras(st);
+    if (!dump.empty()) dump_solution(dump, w, M, N);
+    return 0;
+  }
+
+  // ---- GPU (stage 4) ----
+  const int ndev = pb_cuda_device_count();
+  if (ndev < 1) {
+    std::cerr << "error: no CUDA device; use --stage 0 or --stage 1 for the CPU solvers\n";
+    return 1;
+  }
+  int nranks = virt ? (Px > 0 ? Px * Py : gpus) : gpus;
+  if (Px == 0) pb_choose_proc_grid(nranks, &Px, &Py);
+  if (Px * Py != nranks) {
+    std::cerr << "error: --grid " << Px << "x" << Py << " does not match " << nranks << " ranks\n";
+    return 2;
+  }
+  if (!virt && gpus > ndev) {
+    std::cerr << "error: " << gpus << " GPUs requested, " << ndev << " visible\n";
+    return 1;
+  }
+  std::cout << "MPI + CUDA 2D run with " << nranks << " processes; M=" << M << ", N=" << N << std::endl;
+
+  const double t_before_solver = now_s();
+  pb_stats st{};
+  std::vector<double> w;
+  int rc = 0;
+  if (virt || nranks == 1) {
+    pb_solver* s = pb_solver_create(M, N, Px, Py, 0, nranks, 0);
+    if (!s || pb_solver_finalize(s) != 0) { std::cerr << "error: " << pb_last_error() << "\n"; return 1; }
+    rc = pb_solver_solve(s, &opt, nullptr, &st);
+    if (rc == 0 && !dump.empty()) {
+      w.assign((size_t)(M + 1) * (N + 1), 0.0);
+      rc = pb_solver_copy_solution(s, w.data(), nullptr);
+    }
+    pb_solver_destroy(s);
+  } else {
+    std::vector<int> devs(nranks);
+    for (int r = 0; r < nranks; ++r) devs[r] = r;
+    pb_group* g = pb_group_create(M, N, Px, Py, devs.data(), nranks);
+    if (!g) { std::cerr << "error: " << pb_last_error() << "\n"; return 1; }
+    rc = pb_group_solve(g, &opt, &st);
+    if (rc == 0 && !dump.empty()) {
+      w.assign((size_t)(M + 1) * (N + 1), 0.0);
+      rc = pb_group_copy_solution(g, w.data());
+    }
+    pb_group_destroy(g);
+  }
+  if (rc != 0) { std::cerr << "error: " << pb_last_error() << "\n"; return 1; }
+  const double t_after_solver = now_s();
+
+  if (st.status == PB_STATUS_CONVERGED)
+    std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < " << opt.delta << ").\n";
+  else if (st.status == PB_STATUS_WATCHDOG)
+    std::cout << "Aborted: a device-side wait timed out.\n";
+  std::cout << "   GPU compute time (Ap + D^{-1}r, max over ranks) ~ " << st.t_gpu << " s\n";
+  std::cout << "   Host<->Device copy time (max over ranks)        ~ " << st.t_copy << " s\n";
+  std::cout << "   MPI halo exchange time (max over ranks)         ~ " << st.t_comm << " s\n";
+  std::cout << "   Preconditioner CPU part time (max over ranks)   ~ " << st.t_precond << " s\n";
+  std::cout << "   Dot products time (max over ranks)              ~ " << st.t_dot << " s\n";
+  const double time_init = t_before_solver - t_program_start, time_solver = t_after_solver - t_before_solver;
+  std::cout << "M=" << M << ", N=" << N << " | Iter=" << st.iters << " | Total Time=" << std::fixed
+            << std::setprecision(6) << (time_init + time_solver) << " s\n";
+  std::cout << "   Init time (program)      ~ " << time_init << " s\n";
+  std::cout << "   Solver time (MPI+CUDA)   ~ " << time_solver << " s\n";
+  std::cout << "   Finalization time        ~ " << 0.0 << " s\n";
+  std::cout.flush();
+  if (extras) {
+    std::printf("   Device solve time (assembly + PCG + error report) ~ %.6f s\n", st.seconds);
+    print_extras(st);
+  }
+  if (!dump.empty()) dump_solution(dump, w, M, N);
+  return st.status == PB_STATUS_WATCHDOG ? 3 : 0;
+}

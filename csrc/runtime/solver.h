@@ -61,6 +61,9 @@ class Solver {
   void finalize();  // all peers known -> build and upload the contexts
 
   void solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out);
+  // the two halves of solve(): enqueue everything without host synchronisation / wait and read the report
+  void enqueue(const SolveOptions& opt, cudaStream_t stream);
+  void collect(cudaStream_t stream, pb_stats* out);
   // dense (M+1) x (N+1) host field from the local ranks' blocks (other ranks' nodes are left untouched)
   void copy_solution_to_host(double* full, cudaStream_t stream);
   // dense nx x ny device copy of one local block's owned nodes
@@ -91,6 +94,7 @@ class Solver {
   cudaEvent_t ev_[4];
   int sm_count_ = 148;
   int last_ctas_per_rank_ = 0;
+  int last_method_ = 0;
   long long last_launches_ = 0;
 };
 

@@ -64,10 +64,11 @@ void Solver::solve_steps(const SolveOptions& opt, cudaStream_t stream) {
   }
 }
 
-void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) {
+void Solver::enqueue(const SolveOptions& opt, cudaStream_t stream) {
   if (!finalized_) throw std::runtime_error("Solver::solve before finalize()");
   PB_CUDA_CHECK(cudaSetDevice(device_));
   last_launches_ = 0;
+  last_method_ = opt.method;
   // 1. options: pinned host -> device (the only input of a solve besides M, N fixed at creation)
   pinned_opts_->delta = opt.delta;
   pinned_opts_->max_iter = opt.max_iter >= 0 ? opt.max_iter : (long long)(grid_.M - 1) * (long long)(grid_.N - 1);
@@ -95,8 +96,11 @@ void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) 
   // 3. results: device -> pinned host
   for (int l = 0; l < nlocal(); ++l)
     PB_CUDA_CHECK(cudaMemcpyAsync(pinned_ctl_ + l, control(l), sizeof(Control), cudaMemcpyDeviceToHost, stream));
-  PB_CUDA_CHECK(cudaStreamSynchronize(stream));
+}
 
+void Solver::collect(cudaStream_t stream, pb_stats* out) {
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  PB_CUDA_CHECK(cudaStreamSynchronize(stream));
   if (!out) return;
   std::memset(out, 0, sizeof(*out));
   float ms_asm = 0, ms_iter = 0, ms_err = 0;
@@ -127,7 +131,7 @@ void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) 
   out->seconds = 1e-3 * (double)(ms_asm + ms_iter + ms_err);
   out->t_assemble = 1e-3 * ms_asm;
   out->t_iterations = 1e-3 * ms_iter;
-  if (opt.method == kMethodPersistent) {
+  if (last_method_ == kMethodPersistent) {
     out->t_gpu = 1e-9 * (double)(t_ab + t_c);
     out->t_dot = 1e-9 * (double)(t_r1 + t_r2 + t_init);
     out->t_comm = nranks() > 1 ? 1e-9 * (double)(t_r1 + t_r2) : 0.0;
@@ -136,6 +140,11 @@ void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) 
     out->t_gpu = 1e-3 * ms_iter;
   }
   out->t_copy = 0.0;
+}
+
+void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) {
+  enqueue(opt, stream);
+  collect(stream, out);
 }
 
 void Solver::gather_block(int l, double* dev_out, long long ld, cudaStream_t stream) {

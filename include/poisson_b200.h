@@ -133,6 +133,15 @@ int pb_solver_copy_solution(pb_solver* s, double* host_full /* (M+1)*(N+1) */, v
 int pb_solver_gather_block(pb_solver* s, int local_idx, void* dev_out, long long ld, void* cuda_stream);
 int pb_solver_info(pb_solver* s, int* ctas_per_rank, long long* launches, long long* h2d_bytes, long long* d2h_bytes);
 
+/* ---- single-process multi-GPU group: one rank per listed device, peer access inside the process.
+ *      Used by the CLI and by solve(..., gpus=G) when not running under a multi-process launcher. ---- */
+typedef struct pb_group pb_group;
+pb_group* pb_group_create(int M, int N, int Px, int Py, const int* devices, int ndevices);
+void pb_group_destroy(pb_group* g);
+int pb_group_solve(pb_group* g, const pb_solve_options* opt, pb_stats* stats);
+int pb_group_copy_solution(pb_group* g, double* host_full /* (M+1)*(N+1) */);
+pb_solver* pb_group_solver(pb_group* g, int rank); /* borrowed */
+
 /* kernel-level step API (library-collective baseline: the caller runs NCCL / gloo between the launches) */
 int pb_step_set_options(pb_solver* s, int norm, double delta, long long max_iter, void* cuda_stream);
 int pb_step_assemble(pb_solver* s, int local_idx, void* cuda_stream);

@@ -38,6 +38,7 @@ LIB_SOURCES = [
     "runtime/fabric.cu",
     "runtime/solver.cu",
     "runtime/solver_run.cu",
+    "runtime/group.cu",
     "api/c_api_cuda.cu",
 ]
 CLI_SOURCES = ["cli/main.cpp"]
