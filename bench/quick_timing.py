@@ -12,15 +12,16 @@ def main():
     grids = [(800, 1200), (4096, 4096)] if len(sys.argv) < 3 else [(int(sys.argv[1]), int(sys.argv[2]))]
     for M, N in grids:
         s = GpuSolver(M, N)
-        for method in ("persistent", "step_fused"):
+        for method in ("persistent", "persistent_ldg", "step_fused"):
             for exact in (True, False):
-                for cps in ((1, 2, 3, 4) if method == "persistent" else (0,)):
+                for cps in ((32, 16) if method == "persistent" else (2,) if method == "persistent_ldg" else (0,)):
                     best = None
                     for rep in range(2):
-                        r = s.solve(method=method, exact_div=exact, ctas_per_sm=cps)
+                        r = s.solve(method=method, exact_div=exact, ctas_per_sm=cps if method != "persistent" else 0,
+                                    tile_rows=cps if method == "persistent" else 0)
                         if best is None or r["seconds"] < best["seconds"]:
                             best = r
-                    print(json.dumps({"grid": [M, N], "method": method, "exact": exact, "ctas_per_sm": cps,
+                    print(json.dumps({"grid": [M, N], "method": method, "exact": exact, "ctas_per_sm_or_tile_rows": cps,
                                       "ctas": best["ctas_per_rank"], "iters": best["iters"],
                                       "seconds": round(best["seconds"], 5),
                                       "us_per_iter": round(1e6 * best["t_iterations"] / max(1, best["iters"]), 2),

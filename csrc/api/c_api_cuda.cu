@@ -86,6 +86,7 @@ int pb_solver_solve(pb_solver* s, const pb_solve_options* o, void* stream, pb_st
     opt.exact_div = o->exact_div;
     opt.ctas_per_sm = o->ctas_per_sm;
     opt.error_report = o->error_report;
+    opt.tile_rows = o->tile_rows;
     opt.watchdog_s = o->watchdog_s;
     s->impl.solve(opt, as_stream(stream), stats);
   });
@@ -145,6 +146,7 @@ int pb_group_solve(pb_group* g, const pb_solve_options* o, pb_stats* stats) {
     opt.exact_div = o->exact_div;
     opt.ctas_per_sm = o->ctas_per_sm;
     opt.error_report = o->error_report;
+    opt.tile_rows = o->tile_rows;
     opt.watchdog_s = o->watchdog_s;
     g->impl.solve(opt, stats);
   });

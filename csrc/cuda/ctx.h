@@ -70,6 +70,7 @@ struct RankCtx {
   unsigned long long* slots;
   unsigned long long* peer_slots[kMaxRanks];
   Control* ctl;
+  const void* tmaps;  // CUtensorMap[2][12] in device memory (TMA persistent kernel), see persistent_tma.cu
   int sys_scope;  // 1: some peer lives on another device, fences must be system-wide
   // tiling of the block for the stencil phase
   int tiles_x, tiles_y;

@@ -19,6 +19,12 @@ size_t persistent_smem_bytes();
 int persistent_max_ctas_per_sm(bool exact);
 cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, bool exact, cudaStream_t stream);
 
+// KP-TMA (persistent_tma.cu): tile_rows is 32 (2 stages) or 16 (4 stages)
+cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, bool exact,
+                                  cudaStream_t stream);
+bool build_tensor_maps(const RankCtx& h_ctx, int tile_rows, void* out12);
+size_t tensor_map_bytes();
+
 // step-wise kernels (step_kernels.cu); every kernel returns immediately when Control::status is not
 // PB_STATUS_RUNNING, so the host may enqueue iterations ahead of the stop test.
 enum StepPhase : int { kStepInit = 0, kStepAlpha = 1, kStepBeta = 2 };
@@ -37,9 +43,5 @@ cudaError_t launch_pack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, double
                               cudaStream_t stream);
 cudaError_t launch_unpack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, const double* recvbuf, int stride,
                                 cudaStream_t stream);
-
-// TMA variant of phase AB (tma_stencil.cu)
-cudaError_t launch_step_stencil_tma(const RankCtx* d_ctx, const RankCtx& h_ctx, const void* tensor_maps, bool exact,
-                                    cudaStream_t stream);
 
 }  // namespace pb

@@ -1,0 +1,394 @@
+// persistent_tma.cu -- KP-TMA: the persistent cooperative PCG loop with TMA-fed, multi-stage tile pipelines.
+//
+// Same algorithm and cross-rank protocol as persistent.cu; what changes is how a CTA moves data.  Each
+// phase is a software pipeline over the CTA's tiles: one elected thread issues `cp.async.bulk.tensor.2d`
+// loads for tile j+S-1 (all operand boxes of the tile land in one shared-memory stage and complete on one
+// mbarrier) while all warps compute tile j out of shared memory.  A stage holds
+//     phase AB: r, D, p_old boxes of (TX+2) x (TY+2) (tile + ring), a box (TX+1) x TY, b box TX x (TY+2)
+//     phase C : w, p, r, Ap, D boxes of TX x TY
+// so one SM keeps S-1 complete tiles (45-88 KB each) in flight without spending registers on it, which is
+// what a bandwidth-bound fp64 stencil needs on a part with ~40 KB/SM of latency-bandwidth product.
+// The TMA unit also does the address generation for the misaligned ring boxes and zero-fills the part of
+// a box that lies outside the array (partial tiles at the block edge).
+//
+// Replaces the same reference pieces as persistent.cu (S4:846-942, kernels S4:507-676).
+#include "launch.h"
+#include "phases.cuh"
+#include "tma_utils.cuh"
+
+namespace pb {
+
+enum TmaMap : int { kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, kMapW, kMapP0, kMapP1, kMapR, kMapAp, kMapD };
+
+template <int TX>
+struct TmaCfg {
+  static constexpr int TY = kTileY;
+  static constexpr int ER = TX + 2, EC = TY + 2;
+  static constexpr int kExtBytes = ((ER * EC * 8 + 127) / 128) * 128;
+  static constexpr int kABytes = (TX + 1) * TY * 8;
+  static constexpr int kBBytes = TX * EC * 8;
+  static constexpr int kTileBytes = TX * TY * 8;
+  static constexpr int kStageAB = 3 * kExtBytes + kABytes + kBBytes;
+  static constexpr int kStageC = 5 * kTileBytes;
+  static constexpr int kStageBytes = kStageAB > kStageC ? kStageAB : kStageC;
+  static constexpr int kStages = TX >= 32 ? 2 : 4;
+  // transaction bytes = full boxes, out-of-bounds parts included
+  static constexpr uint32_t kTxAB = 3u * ER * EC * 8u + (uint32_t)kABytes + (uint32_t)kBBytes;
+  static constexpr uint32_t kTxC = 5u * (uint32_t)kTileBytes;
+  static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 128;
+};
+
+template <int TX, bool EXACT>
+__global__ void __launch_bounds__(kThreads, 1)
+pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant) {
+  using Cfg = TmaCfg<TX>;
+  constexpr int TY = Cfg::TY, EC = Cfg::EC, S = Cfg::kStages;
+  __shared__ RankCtx c;
+  __shared__ double s_red[80];
+  __shared__ __align__(8) uint64_t s_bar[S];
+  extern __shared__ __align__(128) unsigned char s_dyn[];
+
+  const int vrank = blockIdx.x / ctas_per_rank;
+  const int cta = blockIdx.x - vrank * ctas_per_rank;
+  const int ncta = ctas_per_rank;
+  {
+    const int* src = reinterpret_cast<const int*>(ctxs + vrank);
+    int* dst = reinterpret_cast<int*>(&c);
+    for (int i = threadIdx.x; i < (int)(sizeof(RankCtx) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) mbar_init(&s_bar[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  unsigned char* stage_base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(s_dyn) + 127) & ~uintptr_t(127));
+  const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * 12;
+  if (threadIdx.x < 12) tma_prefetch_descriptor(maps + threadIdx.x);
+
+  Control* ctl = c.ctl;
+  const int tiles_y = (c.ny + TY - 1) / TY;
+  const int ntiles = ((c.nx + TX - 1) / TX) * tiles_y;
+  const int nmine = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
+  const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
+  const bool timing = (cta == 0 && threadIdx.x == 0);
+  const int S_pitch = c.pitch;
+
+  unsigned int seq = ctl->red_seq, arrive_target = 0;
+  const double delta = ctl->delta;
+  const long long max_iter = ctl->max_iter;
+  const int norm = ctl->norm;
+  const double h1h2 = c.g.h1h2, h1 = c.g.h1, h2 = c.g.h2;
+  const double c1 = -1.0 / h1, c2 = -1.0 / h2, ih1 = 1.0 / h1, ih2 = 1.0 / h2;
+
+  unsigned int n_issued = 0, n_consumed = 0;  // uniform across the CTA
+
+  auto tile_origin = [&](int j, int& li0, int& lj0) {
+    const int t = cta + j * ncta;
+    const int tx = t / tiles_y, ty = t - tx * tiles_y;
+    li0 = 1 + tx * TX;
+    lj0 = 1 + ty * TY;
+  };
+  // one elected thread: arm the stage barrier and issue every box of tile j
+  auto issue_ab = [&](int j, int cur) {
+    if (threadIdx.x == 0) {
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      const unsigned int st = n_issued % S;
+      unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
+      uint64_t* bar = &s_bar[st];
+      fence_proxy_async_smem();
+      mbar_arrive_expect_tx(bar, Cfg::kTxAB);
+      const int x = kColOff + lj0 - 1, y = li0 - 1;
+      tma_load_2d(sb, maps + kMapRExt, x, y, bar);
+      tma_load_2d(sb + Cfg::kExtBytes, maps + kMapDExt, x, y, bar);
+      tma_load_2d(sb + 2 * Cfg::kExtBytes, maps + (cur ? kMapP1Ext : kMapP0Ext), x, y, bar);
+      tma_load_2d(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 1, y + 1, bar);
+      tma_load_2d(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 1, y + 1, bar);
+    }
+    ++n_issued;
+  };
+  auto issue_c = [&](int j, int pbuf) {
+    if (threadIdx.x == 0) {
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      const unsigned int st = n_issued % S;
+      unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
+      uint64_t* bar = &s_bar[st];
+      fence_proxy_async_smem();
+      mbar_arrive_expect_tx(bar, Cfg::kTxC);
+      const int x = kColOff + lj0, y = li0;
+      tma_load_2d(sb, maps + kMapW, x, y, bar);
+      tma_load_2d(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar);
+      tma_load_2d(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar);
+      tma_load_2d(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar);
+      tma_load_2d(sb + 4 * Cfg::kTileBytes, maps + kMapD, x, y, bar);
+    }
+    ++n_issued;
+  };
+  auto wait_stage = [&]() -> unsigned char* {
+    const unsigned int st = n_consumed % S;
+    mbar_wait(&s_bar[st], (n_consumed / S) & 1u);
+    return stage_base + (size_t)st * Cfg::kStageBytes;
+  };
+
+  unsigned long long t_prev = timing ? globaltimer_ns() : 0ull, t_start = t_prev;
+  unsigned long long t_ab = 0, t_c = 0, t_r1 = 0, t_r2 = 0, t_init = 0;
+#define PB_STAMP(acc)                                 \
+  if (timing) {                                       \
+    const unsigned long long now_ = globaltimer_ns(); \
+    acc += now_ - t_prev;                             \
+    t_prev = now_;                                    \
+  }
+
+  // ---- init: zr_old = (D^-1 r, r); plain loads, executed once ----
+  double zr_old;
+  {
+    double v[1] = {0.0};
+    const int nt32 = c.tiles_x * c.tiles_y;
+    for (int t = cta; t < nt32; t += ncta) v[0] += dot_zr_tile(c, t);
+    ++seq;
+    arrive_target += ncta;
+    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+    if (!rr.ok) {
+      if (threadIdx.x == 0 && cta == 0) {
+        ctl->status = PB_STATUS_WATCHDOG;
+        ctl->red_seq = seq;
+      }
+      return;
+    }
+    zr_old = rr.v[0] * h1h2;
+  }
+  PB_STAMP(t_init);
+
+  int cur = 0;
+  double beta = 0.0, alpha = 0.0, denom = 0.0, diff_norm = 0.0;
+  int status = PB_STATUS_MAXITER;
+  long long k = 0;
+  for (k = 1; k <= max_iter; ++k) {
+    double* pout = c.p[cur ^ 1];
+    // ======================= phase AB =======================
+    double acc_ab = 0.0;
+    if (threadIdx.x == 0) fence_proxy_async();  // global data acquired through the last reduction -> TMA reads
+    for (int j = 0; j < S - 1 && j < nmine; ++j) issue_ab(j, cur);
+    for (int j = 0; j < nmine; ++j) {
+      if (j + S - 1 < nmine) issue_ab(j + S - 1, cur);
+      unsigned char* sb = wait_stage();
+      double* s_r = reinterpret_cast<double*>(sb);
+      double* s_D = reinterpret_cast<double*>(sb + Cfg::kExtBytes);
+      double* s_p = reinterpret_cast<double*>(sb + 2 * Cfg::kExtBytes);
+      const double* s_a = reinterpret_cast<const double*>(sb + 3 * Cfg::kExtBytes);
+      const double* s_b = reinterpret_cast<const double*>(sb + 3 * Cfg::kExtBytes + Cfg::kABytes);
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+      // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory
+      for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) {
+        const int row = e / EC, col = e - row * EC;
+        if (col >= cy + 2) continue;
+        const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
+        if (!(row_in || col_in)) continue;
+        const double v = safe_div(s_r[e], s_D[e]) + beta * s_p[e];
+        s_p[e] = v;
+        const int li = li0 - 1 + row, lj = lj0 - 1 + col;
+        const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
+        if ((row_in && col_in) || ring) pout[(size_t)li * S_pitch + (lj + kColOff)] = v;
+      }
+      __syncthreads();
+      // 2. Ap = A p_new on the owned nodes of the tile
+      {
+        const int col = threadIdx.x % TY + 1;
+        if (col <= cy) {
+          for (int row = threadIdx.x / TY + 1; row <= cx; row += kThreads / TY) {
+            const double* s = s_p + row * EC + col;
+            const double pc = s[0], pim = s[-EC], pip = s[EC], pjm = s[-1], pjp = s[1];
+            const double a_c = s_a[(row - 1) * TY + (col - 1)], a_ip = s_a[row * TY + (col - 1)];
+            const double b_c = s_b[(row - 1) * EC + (col - 1)], b_jp = s_b[(row - 1) * EC + col];
+            double v;
+            if (EXACT) {
+              v = stencil_literal(pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp, h1, h2, c1, c2);
+            } else {
+              const double ax = c1 * ((a_ip * (pip - pc)) * ih1 - (a_c * (pc - pim)) * ih1);
+              const double ay = c2 * ((b_jp * (pjp - pc)) * ih2 - (b_c * (pc - pjm)) * ih2);
+              v = ax + ay;
+            }
+            c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
+            acc_ab += v * pc;
+          }
+        }
+      }
+      __syncthreads();  // stage free
+      ++n_consumed;
+    }
+    PB_STAMP(t_ab);
+    {
+      double v[1] = {acc_ab};
+      ++seq;
+      arrive_target += ncta;
+      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+      PB_STAMP(t_r1);
+      if (!rr.ok) {
+        status = PB_STATUS_WATCHDOG;
+        break;
+      }
+      denom = rr.v[0] * h1h2;
+    }
+    if (fabs(denom) < kBreakdownTol) {
+      status = PB_STATUS_BREAKDOWN;
+      break;
+    }
+    alpha = zr_old / denom;
+    // ======================= phase C =======================
+    double acc_d = 0.0, acc_zr = 0.0;
+    if (threadIdx.x == 0) fence_proxy_async();
+    for (int j = 0; j < S - 1 && j < nmine; ++j) issue_c(j, cur ^ 1);
+    for (int j = 0; j < nmine; ++j) {
+      if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
+      unsigned char* sb = wait_stage();
+      const double* s_w = reinterpret_cast<const double*>(sb);
+      const double* s_p = reinterpret_cast<const double*>(sb + Cfg::kTileBytes);
+      const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
+      const double* s_Ap = reinterpret_cast<const double*>(sb + 3 * Cfg::kTileBytes);
+      const double* s_D = reinterpret_cast<const double*>(sb + 4 * Cfg::kTileBytes);
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+      const int col = threadIdx.x % TY;
+      if (col < cy) {
+        for (int row = threadIdx.x / TY; row < cx; row += kThreads / TY) {
+          const int e = row * TY + col;
+          const int li = li0 + row, lj = lj0 + col;
+          const size_t g = (size_t)li * S_pitch + (lj + kColOff);
+          const double w_old = s_w[e];
+          const double w_new = w_old + alpha * s_p[e];
+          const double r_new = s_r[e] - alpha * s_Ap[e];
+          c.w[g] = w_new;
+          c.r[g] = r_new;
+          const double d = w_new - w_old;
+          acc_d += d * d;
+          acc_zr += safe_div(r_new, s_D[e]) * r_new;
+          if (li == 1 && c.nbr_r[kXm])
+            c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
+          if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
+          if (lj == 1 && c.nbr_r[kYm])
+            c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
+          if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+        }
+      }
+      __syncthreads();  // stage free
+      ++n_consumed;
+    }
+    PB_STAMP(t_c);
+    double zr_new;
+    {
+      double v[2] = {acc_d, acc_zr};
+      ++seq;
+      arrive_target += ncta;
+      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, has_nbr);
+      PB_STAMP(t_r2);
+      if (!rr.ok) {
+        status = PB_STATUS_WATCHDOG;
+        break;
+      }
+      diff_norm = norm == PB_NORM_WEIGHTED ? sqrt(rr.v[0] * h1h2) : sqrt(rr.v[0]);
+      zr_new = rr.v[1] * h1h2;
+    }
+    cur ^= 1;
+    if (diff_norm < delta) {
+      status = PB_STATUS_CONVERGED;
+      break;
+    }
+    beta = zr_new / zr_old;
+    zr_old = zr_new;
+  }
+  if (k > max_iter) k = max_iter;
+
+  if (cta == 0 && threadIdx.x == 0) {
+    ctl->iter = (int)k;
+    ctl->status = status;
+    ctl->diff_norm = diff_norm;
+    ctl->alpha = alpha;
+    ctl->beta = beta;
+    ctl->denom = denom;
+    ctl->zr_old = zr_old;
+    ctl->cur = cur;
+    ctl->red_seq = seq;
+    ctl->t_ab = t_ab;
+    ctl->t_c = t_c;
+    ctl->t_red1 = t_r1;
+    ctl->t_red2 = t_r2;
+    ctl->t_init = t_init;
+    ctl->t_total = globaltimer_ns() - t_start;
+  }
+#undef PB_STAMP
+}
+
+// ---------------------------------------------------------------------------------------------------
+template <int TX, bool EXACT>
+static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, cudaStream_t stream) {
+  const void* fn = (const void*)pcg_persistent_tma_kernel<TX, EXACT>;
+  const size_t smem = TmaCfg<TX>::kSmemBytes;
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant};
+  return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
+}
+
+cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, bool exact,
+                                  cudaStream_t stream) {
+  if (tile_rows == 32)
+    return exact ? launch_variant<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, stream)
+                 : launch_variant<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
+  return exact ? launch_variant<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, stream)
+               : launch_variant<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
+}
+
+// Host side: the twelve tensor maps of one rank for one tile height.  The driver entry point is fetched
+// through the runtime so that the library has no link-time dependency on libcuda.
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+static bool encode(CUtensorMap* m, double* base, int rows, int pitch, int box_cols, int box_rows) {
+  if (!encode_fn()) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(double)};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+bool build_tensor_maps(const RankCtx& h, int tile_rows, void* out12) {
+  CUtensorMap* m = static_cast<CUtensorMap*>(out12);
+  const int rows = h.nx + 2, P = h.pitch, TX = tile_rows, TY = kTileY;
+  bool ok = true;
+  ok &= encode(m + kMapRExt, h.r, rows, P, TY + 2, TX + 2);
+  ok &= encode(m + kMapDExt, h.D, rows, P, TY + 2, TX + 2);
+  ok &= encode(m + kMapP0Ext, h.p[0], rows, P, TY + 2, TX + 2);
+  ok &= encode(m + kMapP1Ext, h.p[1], rows, P, TY + 2, TX + 2);
+  ok &= encode(m + kMapA, h.a, rows, P, TY, TX + 1);
+  ok &= encode(m + kMapB, h.b, rows, P, TY + 2, TX);
+  ok &= encode(m + kMapW, h.w, rows, P, TY, TX);
+  ok &= encode(m + kMapP0, h.p[0], rows, P, TY, TX);
+  ok &= encode(m + kMapP1, h.p[1], rows, P, TY, TX);
+  ok &= encode(m + kMapR, h.r, rows, P, TY, TX);
+  ok &= encode(m + kMapAp, h.Ap, rows, P, TY, TX);
+  ok &= encode(m + kMapD, h.D, rows, P, TY, TX);
+  return ok;
+}
+
+size_t tensor_map_bytes() { return sizeof(CUtensorMap); }
+
+}  // namespace pb

@@ -57,7 +57,7 @@ DeviceGroup::~DeviceGroup() {
 }
 
 void DeviceGroup::solve(const SolveOptions& opt, pb_stats* out) {
-  if (opt.method != kMethodPersistent && solvers_.size() > 1)
+  if (opt.method != kMethodPersistent && opt.method != kMethodPersistentLdg && solvers_.size() > 1)
     throw std::runtime_error("DeviceGroup: only the persistent method runs on several devices");
   for (size_t r = 0; r < solvers_.size(); ++r) solvers_[r]->enqueue(opt, streams_[r]);
   std::vector<pb_stats> st(solvers_.size());

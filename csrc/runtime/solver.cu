@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstddef>
 #include <cstring>
+#include <vector>
 
 #include "../api/error.h"
 #include "../cuda/launch.h"
@@ -38,6 +39,7 @@ Solver::Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int dev
     peer_base_[first_rank + l] = base;
   }
   PB_CUDA_CHECK(cudaMalloc(&dctx_, sizeof(RankCtx) * nlocal));
+  PB_CUDA_CHECK(cudaMalloc(&dmaps_, tensor_map_bytes() * 24 * nlocal));
   PB_CUDA_CHECK(cudaMallocHost(&pinned_opts_, sizeof(DeviceOptions)));
   PB_CUDA_CHECK(cudaMallocHost(&pinned_ctl_, sizeof(Control) * nlocal));
   for (auto& e : ev_) PB_CUDA_CHECK(cudaEventCreate(&e));
@@ -50,6 +52,7 @@ Solver::~Solver() {
   for (void* p : opened_ipc_) cudaIpcCloseMemHandle(p);
   for (char* a : arenas_) cudaFree(a);
   if (dctx_) cudaFree(dctx_);
+  if (dmaps_) cudaFree(dmaps_);
   if (pinned_opts_) cudaFreeHost(pinned_opts_);
   if (pinned_ctl_) cudaFreeHost(pinned_ctl_);
   for (auto& e : ev_) cudaEventDestroy(e);
@@ -122,8 +125,18 @@ void Solver::finalize() {
     c.sys_scope = nlocal() != nranks() ? 1 : 0;
     c.tiles_x = (b.nx + kTileX - 1) / kTileX;
     c.tiles_y = (b.ny + kTileY - 1) / kTileY;
+    c.tmaps = dmaps_ + (size_t)l * 24 * tensor_map_bytes();
     hctx_.push_back(c);
   }
+  // tensor maps for both tile heights (host-encoded, copied once)
+  std::vector<char> hmaps(tensor_map_bytes() * 24 * nlocal() + 64);
+  char* hm = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(hmaps.data()) + 63) & ~uintptr_t(63));
+  for (int l = 0; l < nlocal(); ++l) {
+    char* dst = hm + (size_t)l * 24 * tensor_map_bytes();
+    if (!build_tensor_maps(hctx_[l], 32, dst) || !build_tensor_maps(hctx_[l], 16, dst + 12 * tensor_map_bytes()))
+      throw std::runtime_error("cuTensorMapEncodeTiled failed");
+  }
+  PB_CUDA_CHECK(cudaMemcpy(dmaps_, hm, tensor_map_bytes() * 24 * nlocal(), cudaMemcpyHostToDevice));
   PB_CUDA_CHECK(cudaMemcpy(dctx_, hctx_.data(), sizeof(RankCtx) * nlocal(), cudaMemcpyHostToDevice));
   finalized_ = true;
 }

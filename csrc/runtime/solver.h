@@ -14,7 +14,7 @@
 
 namespace pb {
 
-enum Method : int { kMethodPersistent = 0, kMethodStepFused = 1, kMethodStepClassic = 2 };
+enum Method : int { kMethodPersistent = 0, kMethodStepFused = 1, kMethodStepClassic = 2, kMethodPersistentLdg = 3 };
 
 struct SolveOptions {
   int method = kMethodPersistent;
@@ -24,6 +24,7 @@ struct SolveOptions {
   int exact_div = 1;        // literal fp64 divisions (reference association)
   int ctas_per_sm = 0;      // 0 = auto
   int error_report = 1;
+  int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages) or 16 (4 stages); 0 = auto
   double watchdog_s = 0.0;  // 0 = default (20 s)
 };
 
@@ -89,6 +90,7 @@ class Solver {
   std::vector<void*> opened_ipc_;    // bases obtained from cudaIpcOpenMemHandle (to close)
   std::vector<RankCtx> hctx_;
   RankCtx* dctx_ = nullptr;
+  char* dmaps_ = nullptr;  // tensor maps, [nlocal][2 variants][12]
   DeviceOptions* pinned_opts_ = nullptr;
   Control* pinned_ctl_ = nullptr;
   cudaEvent_t ev_[4];

@@ -13,9 +13,10 @@ namespace pb {
 void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   if (!fabric_complete_) throw std::runtime_error("persistent solve needs every rank's arena (open_peer) first");
   const bool exact = opt.exact_div != 0;
-  int per_sm = persistent_max_ctas_per_sm(exact);
+  const bool tma = opt.method == kMethodPersistent;
+  int per_sm = tma ? 1 : persistent_max_ctas_per_sm(exact);
   if (per_sm < 1) throw std::runtime_error("persistent kernel does not fit on an SM");
-  if (opt.ctas_per_sm > 0) per_sm = std::min(per_sm, opt.ctas_per_sm);
+  if (!tma && opt.ctas_per_sm > 0) per_sm = std::min(per_sm, opt.ctas_per_sm);
   int max_tiles = 1;
   for (const RankCtx& c : hctx_) max_tiles = std::max(max_tiles, c.tiles_x * c.tiles_y);
   int ctas = (per_sm * sm_count_) / nlocal();
@@ -24,7 +25,10 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   if (ctas < 1) throw std::runtime_error("too many virtual ranks for one cooperative launch");
   last_ctas_per_rank_ = ctas;
   for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
-  PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
+  if (tma)
+    PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact, stream));
+  else
+    PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;
 }
 
@@ -83,7 +87,7 @@ void Solver::enqueue(const SolveOptions& opt, cudaStream_t stream) {
   for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(launch_assemble(dctx_ + l, hctx_[l], stream));
   last_launches_ += nlocal();
   PB_CUDA_CHECK(cudaEventRecord(ev_[1], stream));
-  if (opt.method == kMethodPersistent)
+  if (opt.method == kMethodPersistent || opt.method == kMethodPersistentLdg)
     solve_persistent(opt, stream);
   else
     solve_steps(opt, stream);
@@ -131,7 +135,7 @@ void Solver::collect(cudaStream_t stream, pb_stats* out) {
   out->seconds = 1e-3 * (double)(ms_asm + ms_iter + ms_err);
   out->t_assemble = 1e-3 * ms_asm;
   out->t_iterations = 1e-3 * ms_iter;
-  if (last_method_ == kMethodPersistent) {
+  if (last_method_ == kMethodPersistent || last_method_ == kMethodPersistentLdg) {
     out->t_gpu = 1e-9 * (double)(t_ab + t_c);
     out->t_dot = 1e-9 * (double)(t_r1 + t_r2 + t_init);
     out->t_comm = nranks() > 1 ? 1e-9 * (double)(t_r1 + t_r2) : 0.0;

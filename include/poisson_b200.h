@@ -102,6 +102,7 @@ typedef struct pb_solver pb_solver;
 #define PB_METHOD_PERSISTENT 0   /* one cooperative launch per solve, fused halo + reductions */
 #define PB_METHOD_STEP_FUSED 1   /* separate launches, fused p-update + stencil (single rank) */
 #define PB_METHOD_STEP_CLASSIC 2 /* separate launches, reference-like 3-kernel structure (single rank) */
+#define PB_METHOD_PERSISTENT_LDG 3 /* persistent kernel with plain global loads instead of TMA pipelines */
 
 typedef struct pb_solve_options {
   int method;
@@ -111,7 +112,7 @@ typedef struct pb_solve_options {
   int exact_div;      /* 1: literal fp64 divisions; 0: reciprocal multiplications in the stencil */
   int ctas_per_sm;    /* 0 = auto */
   int error_report;   /* 1: compute the error against the analytic solution after the solve */
-  int pad;
+  int tile_rows;      /* TMA persistent kernel: 32 (2 pipeline stages) or 16 (4 stages); 0 = auto */
   double watchdog_s;  /* 0 = default (20 s): device-side waits give up after this long */
 } pb_solve_options;
 

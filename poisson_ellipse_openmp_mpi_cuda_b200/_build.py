@@ -34,7 +34,7 @@ LIB_SOURCES = [
     "cuda/assemble.cu",
     "cuda/step_kernels.cu",
     "cuda/persistent.cu",
-    "cuda/tma_stencil.cu",
+    "cuda/persistent_tma.cu",
     "runtime/fabric.cu",
     "runtime/solver.cu",
     "runtime/solver_run.cu",
@@ -100,7 +100,7 @@ def build_native(verbose: bool = False, force: bool = False) -> Path:
     need_link = (not LIB_PATH.exists()) or any(o.stat().st_mtime > LIB_PATH.stat().st_mtime for o in lib_objs)
     if need_link:
         cmd = [_nvcc(), "-shared", *ARCH_FLAGS, "-o", str(LIB_PATH), *map(str, lib_objs), "-Xcompiler",
-               "-fopenmp", "-lcuda", "-lgomp"]
+               "-fopenmp", "-lgomp"]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError(f"link failed: {' '.join(cmd)}\n{res.stdout}\n{res.stderr}")

@@ -70,7 +70,7 @@ class SolveOptions(C.Structure):
         ("exact_div", C.c_int),
         ("ctas_per_sm", C.c_int),
         ("error_report", C.c_int),
-        ("pad", C.c_int),
+        ("tile_rows", C.c_int),
         ("watchdog_s", C.c_double),
     ]
 

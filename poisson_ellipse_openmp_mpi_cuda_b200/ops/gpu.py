@@ -13,7 +13,7 @@ import torch
 from . import _native
 
 NORMS = {"weighted": 0, "unweighted": 1}
-METHODS = {"persistent": 0, "step_fused": 1, "step_classic": 2}
+METHODS = {"persistent": 0, "step_fused": 1, "step_classic": 2, "persistent_ldg": 3}
 STATUS = {0: "max_iter", 1: "converged", 2: "breakdown", 3: "running", 4: "watchdog"}
 ARRAYS = {"w": 0, "r": 1, "p0": 2, "p1": 3, "Ap": 4, "a": 5, "b": 6, "D": 7}
 
@@ -129,11 +129,11 @@ class GpuSolver:
     # -- solve ----------------------------------------------------------------------------------
     def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
               exact_div: bool = True, ctas_per_sm: int = 0, error_report: bool = True, watchdog_s: float = 0.0,
-              stream=None) -> dict:
+              tile_rows: int = 0, stream=None) -> dict:
         if not self._finalized:
             self.finalize()
         opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, int(exact_div), ctas_per_sm,
-                                   int(error_report), 0, watchdog_s)
+                                   int(error_report), tile_rows, watchdog_s)
         st = _native.Stats()
         with torch.cuda.device(self.device):
             _native.check(self.lib.pb_solver_solve(self._h, C.byref(opt), _stream_ptr(stream), C.byref(st)),

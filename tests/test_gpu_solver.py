@@ -46,7 +46,7 @@ def test_assembly_bit_exact(native):
     s.close()
 
 
-@pytest.mark.parametrize("method", ["persistent", "step_fused", "step_classic"])
+@pytest.mark.parametrize("method", ["persistent", "persistent_ldg", "step_fused", "step_classic"])
 @pytest.mark.parametrize("grid", [(10, 10), (40, 40), (160, 160), (400, 600)])
 def test_iteration_parity_single_rank(grid, method):
     s = _solver(*grid)
@@ -80,6 +80,25 @@ def test_virtual_ranks_match_single(grid, pg):
     _check_errors(rm, grid)
     one.close()
     many.close()
+
+
+@pytest.mark.parametrize("tile_rows", [16, 32])
+@pytest.mark.parametrize("pg", [(1, 1), (2, 2)])
+def test_tma_tile_heights(tile_rows, pg):
+    for grid in [(40, 40), (400, 600)]:
+        s = _solver(*grid, *pg)
+        res = s.solve(tile_rows=tile_rows)
+        assert res["iters"] == ITERS_WEIGHTED[grid]
+        _check_errors(res, grid)
+        s.close()
+
+
+@pytest.mark.parametrize("pg", [(1, 2), (2, 2), (2, 4)])
+def test_virtual_ranks_ldg_kernel(pg):
+    s = _solver(160, 160, *pg)
+    res = s.solve(method="persistent_ldg")
+    assert res["iters"] == 183
+    s.close()
 
 
 def test_reciprocal_stencil_keeps_iteration_count():
