@@ -111,7 +111,7 @@ def run_ours(a) -> dict:
             dist.barrier()
             torch.cuda.synchronize()
 
-    kw = dict(exact_div=not a.fast_div, ctas_per_sm=a.ctas_per_sm)
+    kw = dict(div=a.div, tile_rows=a.tile_rows)
     for _ in range(a.warmup):
         flush.fill_(1)
         res = solver.solve(**kw)
@@ -157,7 +157,7 @@ def run_ours(a) -> dict:
                    "global_batch": 1, "seq_len": nodes, "parallelism": f"{solver.grid[0]}x{solver.grid[1]} spatial "
                    "blocks, peer-memory halo + in-kernel reductions", "l2": "512 MiB flush buffer written between "
                    "timed solves; each solve re-assembles all arrays", "method": "persistent cooperative kernel",
-                   "exact_div": not a.fast_div, "ctas_per_rank": info["ctas_per_rank"]},
+                   "div": a.div, "ctas_per_rank": info["ctas_per_rank"]},
         "iterations": iters[-1], "expected_iterations": EXPECTED_ITERS.get((M, N)), "status": res["status_name"],
         "us_per_iter": us_iter, "l2_error_in_D": res["l2_in_D"], "max_error": res["max_abs"],
         "hbm_gbs_model": 112.0 * nodes / (us_iter * 1e-6) / 1e9 / world,
@@ -249,8 +249,10 @@ def main():
     ap.add_argument("--M", type=int, default=M_DEFAULT)
     ap.add_argument("--N", type=int, default=N_DEFAULT)
     ap.add_argument("--grid", default=None, help="PxxPy override of the process grid")
-    ap.add_argument("--fast-div", action="store_true", help="reciprocal multiplications in the stencil")
-    ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--div", default="markstein", choices=["markstein", "true", "recip"],
+                    help="stencil divisions by h1/h2: markstein = correctly rounded 3-instruction sequence (same "
+                         "bits as 'true'), true = IEEE division, recip = multiply by the reciprocal")
+    ap.add_argument("--tile-rows", type=int, default=0)
     a = ap.parse_args()
     out = run_reference(a) if a.impl == "reference" else run_ours(a)
     if out is not None:

@@ -12,12 +12,12 @@ def main():
     grids = [(800, 1200), (4096, 4096)] if len(sys.argv) < 3 else [(int(sys.argv[1]), int(sys.argv[2]))]
     for M, N in grids:
         s = GpuSolver(M, N)
-        for method in ("persistent", "persistent_ldg", "step_fused"):
-            for exact in (True, False):
+        for method in ("persistent",):
+            for exact in ("true", "markstein", "recip"):
                 for cps in ((32, 16) if method == "persistent" else (2,) if method == "persistent_ldg" else (0,)):
                     best = None
                     for rep in range(2):
-                        r = s.solve(method=method, exact_div=exact, ctas_per_sm=cps if method != "persistent" else 0,
+                        r = s.solve(method=method, div=exact, ctas_per_sm=cps if method != "persistent" else 0,
                                     tile_rows=cps if method == "persistent" else 0)
                         if best is None or r["seconds"] < best["seconds"]:
                             best = r

@@ -183,8 +183,8 @@ int pb_step_begin(pb_solver* s, int l, void* st) { PB_STEP(pb::launch_step_begin
 int pb_step_dot_zr(pb_solver* s, int l, void* st) {
   PB_STEP(pb::launch_step_dot_zr(s->impl.device_ctx(l), s->impl.host_ctx(l), as_stream(st)));
 }
-int pb_step_stencil(pb_solver* s, int l, int fuse_p, int exact, void* st) {
-  PB_STEP(pb::launch_step_stencil(s->impl.device_ctx(l), s->impl.host_ctx(l), fuse_p != 0, exact != 0, as_stream(st)));
+int pb_step_stencil(pb_solver* s, int l, int fuse_p, int div, void* st) {
+  PB_STEP(pb::launch_step_stencil(s->impl.device_ctx(l), s->impl.host_ctx(l), fuse_p != 0, div, as_stream(st)));
 }
 int pb_step_update(pb_solver* s, int l, int fuse_p, void* st) {
   PB_STEP(pb::launch_step_update(s->impl.device_ctx(l), s->impl.host_ctx(l), fuse_p != 0, as_stream(st)));
@@ -207,6 +207,11 @@ int pb_step_unpack_edges(pb_solver* s, int l, const void* buf, int stride, void*
 }
 int pb_step_error_report(pb_solver* s, int l, void* st) {
   PB_STEP(pb::launch_error_report(s->impl.device_ctx(l), s->impl.host_ctx(l), as_stream(st)));
+}
+int pb_debug_tma_probe(pb_solver* s, int l, int idx, int mode, int x, int y, unsigned int nbytes, void* out, void* status,
+                       void* st) {
+  PB_STEP(pb::launch_tma_probe(s->impl.host_ctx(l).tmaps, s->impl.host_maps(l), idx, mode, x, y, nbytes, static_cast<double*>(out),
+                               static_cast<int*>(status), as_stream(st)));
 }
 int pb_step_read_control(pb_solver* s, int l, int* iter, int* status, double* diff_norm, void* st) {
   return guarded([&] {

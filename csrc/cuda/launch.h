@@ -14,14 +14,17 @@ cudaError_t launch_error_report(const RankCtx* d_ctx, const RankCtx& h_ctx, cuda
 cudaError_t launch_gather_interior(const double* w, int nx, int ny, int pitch, double* out, long long ld,
                                    cudaStream_t stream);
 
+// `div` everywhere: 0 reciprocal multiply, 1 true division, 2 Markstein (bit-identical to 1), see phases.cuh
 // KP (persistent.cu)
 size_t persistent_smem_bytes();
-int persistent_max_ctas_per_sm(bool exact);
-cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, bool exact, cudaStream_t stream);
+int persistent_max_ctas_per_sm(int div);
+cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int div, cudaStream_t stream);
 
 // KP-TMA (persistent_tma.cu): tile_rows is 32 (2 stages) or 16 (4 stages)
-cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, bool exact,
+cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
                                   cudaStream_t stream);
+cudaError_t launch_tma_probe(const void* dmaps, const void* hmaps, int idx, int mode, int x, int y, unsigned int nbytes,
+                             double* out, int* out_status, cudaStream_t stream);
 bool build_tensor_maps(const RankCtx& h_ctx, int tile_rows, void* out12);
 size_t tensor_map_bytes();
 
@@ -30,7 +33,7 @@ size_t tensor_map_bytes();
 enum StepPhase : int { kStepInit = 0, kStepAlpha = 1, kStepBeta = 2 };
 cudaError_t launch_step_begin(const RankCtx* d_ctx, cudaStream_t stream);  // status = RUNNING, iter = 0
 cudaError_t launch_step_dot_zr(const RankCtx* d_ctx, const RankCtx& h_ctx, cudaStream_t stream);
-cudaError_t launch_step_stencil(const RankCtx* d_ctx, const RankCtx& h_ctx, bool fuse_p, bool exact,
+cudaError_t launch_step_stencil(const RankCtx* d_ctx, const RankCtx& h_ctx, bool fuse_p, int div,
                                 cudaStream_t stream);
 cudaError_t launch_step_update(const RankCtx* d_ctx, const RankCtx& h_ctx, bool fuse_p, cudaStream_t stream);
 cudaError_t launch_step_update_p(const RankCtx* d_ctx, const RankCtx& h_ctx, cudaStream_t stream);

@@ -21,7 +21,7 @@
 
 namespace pb {
 
-template <bool EXACT>
+template <int DIV>
 __global__ void __launch_bounds__(kThreads, 2)
 pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
   __shared__ RankCtx c;
@@ -91,7 +91,7 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
     // ---- phase AB ----
     {
       double v[1] = {0.0};
-      for (int t = cta; t < ntiles; t += ncta) v[0] += phase_ab_tile<true, EXACT>(c, t, beta, pin, pout, s_tile);
+      for (int t = cta; t < ntiles; t += ncta) v[0] += phase_ab_tile<true, DIV>(c, t, beta, pin, pout, s_tile);
       PB_STAMP(t_ab);
       ++seq;
       arrive_target += ncta;
@@ -157,19 +157,22 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
 
 size_t persistent_smem_bytes() { return sizeof(double) * kSmemTile; }
 
-int persistent_max_ctas_per_sm(bool exact) {
+static const void* persistent_fn(int div) {
+  return div == kDivTrue ? (const void*)pcg_persistent_kernel<kDivTrue>
+                         : (div == kDivMarkstein ? (const void*)pcg_persistent_kernel<kDivMarkstein>
+                                                 : (const void*)pcg_persistent_kernel<kDivRecip>);
+}
+
+int persistent_max_ctas_per_sm(int div) {
   int n = 0;
-  if (exact)
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pcg_persistent_kernel<true>, kThreads, persistent_smem_bytes());
-  else
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pcg_persistent_kernel<false>, kThreads, persistent_smem_bytes());
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, persistent_fn(div), kThreads, persistent_smem_bytes());
   return n;
 }
 
-cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, bool exact, cudaStream_t stream) {
+cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int div, cudaStream_t stream) {
   void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank};
   const dim3 grid(nvirt * ctas_per_rank), block(kThreads);
-  const void* fn = exact ? (const void*)pcg_persistent_kernel<true> : (const void*)pcg_persistent_kernel<false>;
+  const void* fn = persistent_fn(div);
   return cudaLaunchCooperativeKernel(fn, grid, block, args, persistent_smem_bytes(), stream);
 }
 

@@ -4,7 +4,8 @@
 // phase is a software pipeline over the CTA's tiles: one elected thread issues `cp.async.bulk.tensor.2d`
 // loads for tile j+S-1 (all operand boxes of the tile land in one shared-memory stage and complete on one
 // mbarrier) while all warps compute tile j out of shared memory.  A stage holds
-//     phase AB: r, D, p_old boxes of (TX+2) x (TY+2) (tile + ring), a box (TX+1) x TY, b box TX x (TY+2)
+//     phase AB: r, D, p_old boxes of (TX+2) x (TY+4) (tile + ring; one more column on each side because a
+//               box must start on a 16-byte boundary), a box (TX+1) x TY, b box TX x (TY+2)
 //     phase C : w, p, r, Ap, D boxes of TX x TY
 // so one SM keeps S-1 complete tiles (45-88 KB each) in flight without spending registers on it, which is
 // what a bandwidth-bound fp64 stencil needs on a part with ~40 KB/SM of latency-bandwidth product.
@@ -23,10 +24,11 @@ enum TmaMap : int { kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, 
 template <int TX>
 struct TmaCfg {
   static constexpr int TY = kTileY;
-  static constexpr int ER = TX + 2, EC = TY + 2;
+  static constexpr int ER = TX + 2, EC = TY + 4;  // ring boxes start one column early: TMA wants 16-byte starts
+  static constexpr int BC = TY + 2;               // b box width
   static constexpr int kExtBytes = ((ER * EC * 8 + 127) / 128) * 128;
   static constexpr int kABytes = (TX + 1) * TY * 8;
-  static constexpr int kBBytes = TX * EC * 8;
+  static constexpr int kBBytes = TX * BC * 8;
   static constexpr int kTileBytes = TX * TY * 8;
   static constexpr int kStageAB = 3 * kExtBytes + kABytes + kBBytes;
   static constexpr int kStageC = 5 * kTileBytes;
@@ -38,11 +40,11 @@ struct TmaCfg {
   static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 128;
 };
 
-template <int TX, bool EXACT>
+template <int TX, int DIV>
 __global__ void __launch_bounds__(kThreads, 1)
 pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant) {
   using Cfg = TmaCfg<TX>;
-  constexpr int TY = Cfg::TY, EC = Cfg::EC, S = Cfg::kStages;
+  constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
   __shared__ double s_red[80];
   __shared__ __align__(8) uint64_t s_bar[S];
@@ -63,12 +65,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   __syncthreads();
   unsigned char* stage_base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(s_dyn) + 127) & ~uintptr_t(127));
   const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * 12;
-  if (threadIdx.x < 12) tma_prefetch_descriptor(maps + threadIdx.x);
 
   Control* ctl = c.ctl;
   const int tiles_y = (c.ny + TY - 1) / TY;
   const int ntiles = ((c.nx + TX - 1) / TX) * tiles_y;
   const int nmine = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
+  const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
   const bool timing = (cta == 0 && threadIdx.x == 0);
   const int S_pitch = c.pitch;
@@ -77,8 +79,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const double delta = ctl->delta;
   const long long max_iter = ctl->max_iter;
   const int norm = ctl->norm;
-  const double h1h2 = c.g.h1h2, h1 = c.g.h1, h2 = c.g.h2;
-  const double c1 = -1.0 / h1, c2 = -1.0 / h2, ih1 = 1.0 / h1, ih2 = 1.0 / h2;
+  const double h1h2 = c.g.h1h2;
+  const StencilConsts K = make_stencil_consts(c.g);
 
   unsigned int n_issued = 0, n_consumed = 0;  // uniform across the CTA
 
@@ -88,23 +90,28 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     li0 = 1 + tx * TX;
     lj0 = 1 + ty * TY;
   };
-  // one elected thread: arm the stage barrier and issue every box of tile j
-  auto issue_ab = [&](int j, int cur) {
+  // Phase-AB loads of tile j into stage `st`.  part 1 = everything that does not depend on the other CTAs'
+  // phase C (D, p, a, b; arms the barrier with the full byte count), part 2 = the r box.
+  auto issue_ab_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2) {
     if (threadIdx.x == 0) {
       int li0, lj0;
       tile_origin(j, li0, lj0);
-      const unsigned int st = n_issued % S;
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
-      fence_proxy_async_smem();
-      mbar_arrive_expect_tx(bar, Cfg::kTxAB);
-      const int x = kColOff + lj0 - 1, y = li0 - 1;
-      tma_load_2d(sb, maps + kMapRExt, x, y, bar);
-      tma_load_2d(sb + Cfg::kExtBytes, maps + kMapDExt, x, y, bar);
-      tma_load_2d(sb + 2 * Cfg::kExtBytes, maps + (cur ? kMapP1Ext : kMapP0Ext), x, y, bar);
-      tma_load_2d(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 1, y + 1, bar);
-      tma_load_2d(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 1, y + 1, bar);
+      const int x = kColOff + lj0 - 2, y = li0 - 1;  // even column: 16-byte aligned box start
+      if (part1) {
+        fence_proxy_async_smem();
+        mbar_arrive_expect_tx(bar, Cfg::kTxAB);
+        tma_load_2d(sb + Cfg::kExtBytes, maps + kMapDExt, x, y, bar);
+        tma_load_2d(sb + 2 * Cfg::kExtBytes, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar);
+        tma_load_2d(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 2, y + 1, bar);
+        tma_load_2d(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 2, y + 1, bar);
+      }
+      if (part2) tma_load_2d(sb, maps + kMapRExt, x, y, bar);
     }
+  };
+  auto issue_ab = [&](int j, int pbuf) {
+    issue_ab_part(j, n_issued % S, pbuf, true, true);
     ++n_issued;
   };
   auto issue_c = [&](int j, int pbuf) {
@@ -125,10 +132,25 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     }
     ++n_issued;
   };
+  bool tma_ok = true;
   auto wait_stage = [&]() -> unsigned char* {
     const unsigned int st = n_consumed % S;
-    mbar_wait(&s_bar[st], (n_consumed / S) & 1u);
+    if (!mbar_wait(&s_bar[st], (n_consumed / S) & 1u)) {
+      if (threadIdx.x == 0) {  // internal error: leave a trace and abandon; the other CTAs run into the watchdog
+        ctl->status = PB_STATUS_TMA_TIMEOUT;
+        ctl->red[0] = (double)n_consumed;
+        ctl->red[1] = (double)cta;
+      }
+      tma_ok = false;
+    }
     return stage_base + (size_t)st * Cfg::kStageBytes;
+  };
+  // nothing may be in flight into shared memory when the CTA exits
+  auto drain = [&]() {
+    while (n_consumed < n_issued && tma_ok) {
+      wait_stage();
+      ++n_consumed;
+    }
   };
 
   unsigned long long t_prev = timing ? globaltimer_ns() : 0ull, t_start = t_prev;
@@ -140,6 +162,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     t_prev = now_;                                    \
   }
 
+  int cur = 0;
+  // Prefetch for the first phase AB.  Everything it reads was written by the assembly kernel (an earlier
+  // launch), so both parts can go out before the initial reduction.
+  for (int j = 0; j < npre; ++j) issue_ab(j, cur);
+
   // ---- init: zr_old = (D^-1 r, r); plain loads, executed once ----
   double zr_old;
   {
@@ -150,6 +177,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     arrive_target += ncta;
     const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
     if (!rr.ok) {
+      drain();
       if (threadIdx.x == 0 && cta == 0) {
         ctl->status = PB_STATUS_WATCHDOG;
         ctl->red_seq = seq;
@@ -160,21 +188,19 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   }
   PB_STAMP(t_init);
 
-  int cur = 0;
   double beta = 0.0, alpha = 0.0, denom = 0.0, diff_norm = 0.0;
   int status = PB_STATUS_MAXITER;
   long long k = 0;
   for (k = 1; k <= max_iter; ++k) {
     double* pout = c.p[cur ^ 1];
-    // ======================= phase AB =======================
+    // ======================= phase AB (tiles 0..npre-1 are already in flight) =======================
     double acc_ab = 0.0;
-    if (threadIdx.x == 0) fence_proxy_async();  // global data acquired through the last reduction -> TMA reads
-    for (int j = 0; j < S - 1 && j < nmine; ++j) issue_ab(j, cur);
-    for (int j = 0; j < nmine; ++j) {
+    for (int j = 0; j < nmine && tma_ok; ++j) {
       if (j + S - 1 < nmine) issue_ab(j + S - 1, cur);
       unsigned char* sb = wait_stage();
-      double* s_r = reinterpret_cast<double*>(sb);
-      double* s_D = reinterpret_cast<double*>(sb + Cfg::kExtBytes);
+      if (!tma_ok) break;
+      const double* s_r = reinterpret_cast<const double*>(sb);
+      const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kExtBytes);
       double* s_p = reinterpret_cast<double*>(sb + 2 * Cfg::kExtBytes);
       const double* s_a = reinterpret_cast<const double*>(sb + 3 * Cfg::kExtBytes);
       const double* s_b = reinterpret_cast<const double*>(sb + 3 * Cfg::kExtBytes + Cfg::kABytes);
@@ -183,8 +209,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
       // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory
       for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) {
-        const int row = e / EC, col = e - row * EC;
-        if (col >= cy + 2) continue;
+        const int row = e / EC, col = e - row * EC - 1;  // col 0 = left ring column of the tile
+        if (col < 0 || col >= cy + 2) continue;
         const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
         if (!(row_in || col_in)) continue;
         const double v = safe_div(s_r[e], s_D[e]) + beta * s_p[e];
@@ -199,18 +225,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         const int col = threadIdx.x % TY + 1;
         if (col <= cy) {
           for (int row = threadIdx.x / TY + 1; row <= cx; row += kThreads / TY) {
-            const double* s = s_p + row * EC + col;
+            const double* s = s_p + row * EC + col + 1;
             const double pc = s[0], pim = s[-EC], pip = s[EC], pjm = s[-1], pjp = s[1];
             const double a_c = s_a[(row - 1) * TY + (col - 1)], a_ip = s_a[row * TY + (col - 1)];
-            const double b_c = s_b[(row - 1) * EC + (col - 1)], b_jp = s_b[(row - 1) * EC + col];
-            double v;
-            if (EXACT) {
-              v = stencil_literal(pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp, h1, h2, c1, c2);
-            } else {
-              const double ax = c1 * ((a_ip * (pip - pc)) * ih1 - (a_c * (pc - pim)) * ih1);
-              const double ay = c2 * ((b_jp * (pjp - pc)) * ih2 - (b_c * (pc - pjm)) * ih2);
-              v = ax + ay;
-            }
+            const double b_c = s_b[(row - 1) * BC + (col - 1)], b_jp = s_b[(row - 1) * BC + col];
+            const double v = stencil_value<DIV>(K, pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp);
             c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
             acc_ab += v * pc;
           }
@@ -219,6 +238,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       __syncthreads();  // stage free
       ++n_consumed;
     }
+    if (!tma_ok) break;
+    // Prefetch for phase C: it reads only what this CTA itself wrote (p_new, Ap) or owns (w, r, D), so its
+    // first tiles can be in flight while the reduction below waits for the slowest CTA / GPU.
+    if (threadIdx.x == 0) fence_proxy_async();  // our generic-proxy global stores -> TMA reads
+    for (int j = 0; j < npre; ++j) issue_c(j, cur ^ 1);
     PB_STAMP(t_ab);
     {
       double v[1] = {acc_ab};
@@ -239,11 +263,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     alpha = zr_old / denom;
     // ======================= phase C =======================
     double acc_d = 0.0, acc_zr = 0.0;
-    if (threadIdx.x == 0) fence_proxy_async();
-    for (int j = 0; j < S - 1 && j < nmine; ++j) issue_c(j, cur ^ 1);
-    for (int j = 0; j < nmine; ++j) {
+    for (int j = 0; j < nmine && tma_ok; ++j) {
       if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
       unsigned char* sb = wait_stage();
+      if (!tma_ok) break;
       const double* s_w = reinterpret_cast<const double*>(sb);
       const double* s_p = reinterpret_cast<const double*>(sb + Cfg::kTileBytes);
       const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
@@ -277,8 +300,19 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       __syncthreads();  // stage free
       ++n_consumed;
     }
+    if (!tma_ok) break;
+    // Prefetch for the next phase AB, part 1: D, a, b are constant and p_new (buffer cur^1, ring included)
+    // was completed before the previous reduction.  The r box waits for the reduction below, because its
+    // ring cells are written by other CTAs / GPUs during this very phase.
+    const unsigned int pre_base = n_issued;
+    if (threadIdx.x == 0) fence_proxy_async();
+    for (int j = 0; j < npre; ++j) {
+      issue_ab_part(j, n_issued % S, cur ^ 1, true, false);
+      ++n_issued;
+    }
     PB_STAMP(t_c);
     double zr_new;
+    bool stop = false;
     {
       double v[2] = {acc_d, acc_zr};
       ++seq;
@@ -287,12 +321,16 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       PB_STAMP(t_r2);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
-        break;
+        stop = true;
       }
       diff_norm = norm == PB_NORM_WEIGHTED ? sqrt(rr.v[0] * h1h2) : sqrt(rr.v[0]);
       zr_new = rr.v[1] * h1h2;
     }
+    // part 2 of the prefetch: everybody's r (ours, our neighbours' ring values) is final and acquired
+    if (threadIdx.x == 0) fence_proxy_async();
+    for (int j = 0; j < npre; ++j) issue_ab_part(j, (pre_base + j) % S, cur ^ 1, false, true);
     cur ^= 1;
+    if (stop) break;
     if (diff_norm < delta) {
       status = PB_STATUS_CONVERGED;
       break;
@@ -301,8 +339,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     zr_old = zr_new;
   }
   if (k > max_iter) k = max_iter;
+  drain();
 
-  if (cta == 0 && threadIdx.x == 0) {
+  if (cta == 0 && threadIdx.x == 0 && tma_ok) {
     ctl->iter = (int)k;
     ctl->status = status;
     ctl->diff_norm = diff_norm;
@@ -323,9 +362,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 }
 
 // ---------------------------------------------------------------------------------------------------
-template <int TX, bool EXACT>
+template <int TX, int DIV>
 static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, cudaStream_t stream) {
-  const void* fn = (const void*)pcg_persistent_tma_kernel<TX, EXACT>;
+  const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV>;
   const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
@@ -333,13 +372,62 @@ static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
 }
 
-cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, bool exact,
+cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
                                   cudaStream_t stream) {
-  if (tile_rows == 32)
-    return exact ? launch_variant<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, stream)
-                 : launch_variant<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
-  return exact ? launch_variant<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, stream)
-               : launch_variant<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
+  if (tile_rows == 32) {
+    if (div == kDivTrue) return launch_variant<32, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
+    if (div == kDivMarkstein) return launch_variant<32, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
+    return launch_variant<32, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
+  }
+  if (div == kDivTrue) return launch_variant<16, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
+  if (div == kDivMarkstein) return launch_variant<16, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
+  return launch_variant<16, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
+}
+
+// Debug / unit-test probe: one box load through a tensor map at (x, y) into shared memory, copied out to
+// `out` (nbytes), out_status = 1 on completion, 2 on timeout.  mode 0: map in global memory; mode 1: same,
+// after a tensormap-proxy acquire fence; mode 2: map passed as a __grid_constant__ kernel parameter.
+template <int MODE>
+__global__ void tma_probe_kernel(const CUtensorMap* gmap, const __grid_constant__ CUtensorMap pmap, int x, int y,
+                                 unsigned int nbytes, double* out, int* out_status) {
+  extern __shared__ __align__(128) unsigned char s_dyn[];
+  __shared__ __align__(8) uint64_t bar;
+  unsigned char* buf = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(s_dyn) + 127) & ~uintptr_t(127));
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const CUtensorMap* map = MODE == 2 ? &pmap : gmap;
+    if (MODE == 1)
+      asm volatile("fence.proxy.tensormap::generic.acquire.gpu [%0], 128;" ::"l"(reinterpret_cast<uint64_t>(gmap)) : "memory");
+    mbar_arrive_expect_tx(&bar, nbytes);
+    tma_load_2d(buf, map, x, y, &bar);
+  }
+  const bool ok = mbar_wait(&bar, 0);
+  if (ok)
+    for (unsigned int i = threadIdx.x; i < nbytes / 8; i += blockDim.x) out[i] = reinterpret_cast<double*>(buf)[i];
+  if (threadIdx.x == 0) *out_status = ok ? 1 : 2;
+}
+
+cudaError_t launch_tma_probe(const void* dmaps, const void* hmaps, int idx, int mode, int x, int y, unsigned int nbytes,
+                             double* out, int* out_status, cudaStream_t stream) {
+  const CUtensorMap* g = static_cast<const CUtensorMap*>(dmaps) + idx;
+  const CUtensorMap p = static_cast<const CUtensorMap*>(hmaps)[idx];
+  const size_t smem = nbytes + 256;
+  cudaError_t e = cudaSuccess;
+  if (mode == 0) {
+    e = cudaFuncSetAttribute(tma_probe_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) tma_probe_kernel<0><<<1, 128, smem, stream>>>(g, p, x, y, nbytes, out, out_status);
+  } else if (mode == 1) {
+    e = cudaFuncSetAttribute(tma_probe_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) tma_probe_kernel<1><<<1, 128, smem, stream>>>(g, p, x, y, nbytes, out, out_status);
+  } else {
+    e = cudaFuncSetAttribute(tma_probe_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) tma_probe_kernel<2><<<1, 128, smem, stream>>>(g, p, x, y, nbytes, out, out_status);
+  }
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 // Host side: the twelve tensor maps of one rank for one tile height.  The driver entry point is fetched
@@ -374,10 +462,10 @@ bool build_tensor_maps(const RankCtx& h, int tile_rows, void* out12) {
   CUtensorMap* m = static_cast<CUtensorMap*>(out12);
   const int rows = h.nx + 2, P = h.pitch, TX = tile_rows, TY = kTileY;
   bool ok = true;
-  ok &= encode(m + kMapRExt, h.r, rows, P, TY + 2, TX + 2);
-  ok &= encode(m + kMapDExt, h.D, rows, P, TY + 2, TX + 2);
-  ok &= encode(m + kMapP0Ext, h.p[0], rows, P, TY + 2, TX + 2);
-  ok &= encode(m + kMapP1Ext, h.p[1], rows, P, TY + 2, TX + 2);
+  ok &= encode(m + kMapRExt, h.r, rows, P, TY + 4, TX + 2);
+  ok &= encode(m + kMapDExt, h.D, rows, P, TY + 4, TX + 2);
+  ok &= encode(m + kMapP0Ext, h.p[0], rows, P, TY + 4, TX + 2);
+  ok &= encode(m + kMapP1Ext, h.p[1], rows, P, TY + 4, TX + 2);
   ok &= encode(m + kMapA, h.a, rows, P, TY, TX + 1);
   ok &= encode(m + kMapB, h.b, rows, P, TY + 2, TX);
   ok &= encode(m + kMapW, h.w, rows, P, TY, TX);

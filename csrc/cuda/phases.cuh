@@ -10,8 +10,8 @@
 //       w += alpha p, r -= alpha Ap, partial sum (w_new - w_old)^2, partial (r/D, r); boundary nodes
 //       additionally store r_new straight into the neighbour GPU's ring (peer store over NVLink).
 //
-// z = r/D is never stored.  fp64 divisions follow the reference's association when EXACT is true; with
-// EXACT false the divisions by h1/h2 become multiplications by correctly rounded reciprocals.
+// z = r/D is never stored and always a true division.  The divisions by h1/h2 inside the stencil follow
+// the DivMode template parameter (see below).
 #pragma once
 #include "device_utils.cuh"
 
@@ -38,10 +38,46 @@ __device__ __forceinline__ TileGeom tile_geom(const RankCtx& c, int tile) {
 
 __device__ __forceinline__ double safe_div(double r, double d) { return d != 0.0 ? r / d : 0.0; }
 
+// How the six divisions by h1 / h2 inside the stencil are evaluated.
+//   kDivTrue      x / h, the compiler's IEEE division (about a dozen fp64 instructions each)
+//   kDivMarkstein q = x*y, q' = fma(fma(-q, h, x), y, q) with y = RN(1/h): by Markstein's theorem q' is the
+//                 correctly rounded quotient, i.e. the same bits as kDivTrue, in three instructions
+//                 (no range fix-up path: operands here are far from overflow / underflow)
+//   kDivRecip     x * y, one rounding differs from x / h in the last bit now and then
+enum DivMode : int { kDivRecip = 0, kDivTrue = 1, kDivMarkstein = 2 };
+
+struct StencilConsts {
+  double h1, h2, c1, c2, ih1, ih2;  // c = -1/h, ih = RN(1/h)
+};
+__device__ __forceinline__ StencilConsts make_stencil_consts(const Grid& g) {
+  StencilConsts k;
+  k.h1 = g.h1, k.h2 = g.h2;
+  k.c1 = -1.0 / g.h1, k.c2 = -1.0 / g.h2;
+  k.ih1 = 1.0 / g.h1, k.ih2 = 1.0 / g.h2;
+  return k;
+}
+
+template <int DIV>
+__device__ __forceinline__ double div_const(double x, double h, double y) {
+  if (DIV == kDivTrue) return x / h;
+  const double q = x * y;
+  if (DIV == kDivRecip) return q;
+  return fma(fma(-q, h, x), y, q);
+}
+
+// (A p) at one node, association of the reference (S4:526-535).
+template <int DIV>
+__device__ __forceinline__ double stencil_value(const StencilConsts& k, double pc, double pim, double pip, double pjm,
+                                                double pjp, double a_c, double a_ip, double b_c, double b_jp) {
+  const double ax = k.c1 * (div_const<DIV>(a_ip * (pip - pc), k.h1, k.ih1) - div_const<DIV>(a_c * (pc - pim), k.h1, k.ih1));
+  const double ay = k.c2 * (div_const<DIV>(b_jp * (pjp - pc), k.h2, k.ih2) - div_const<DIV>(b_c * (pc - pjm), k.h2, k.ih2));
+  return ax + ay;
+}
+
 // Phase AB on one tile; returns this thread's contribution to sum(Ap * p_new).
 // FUSE_P = false: `pin` already holds the direction including its ring (classic path); nothing is
 // written to `pout`.
-template <bool FUSE_P, bool EXACT>
+template <bool FUSE_P, int DIV>
 __device__ __forceinline__ double phase_ab_tile(const RankCtx& c, int tile, double beta, const double* __restrict__ pin,
                                                 double* __restrict__ pout, double* sp) {
   const TileGeom t = tile_geom(c, tile);
@@ -67,9 +103,7 @@ __device__ __forceinline__ double phase_ab_tile(const RankCtx& c, int tile, doub
   }
   __syncthreads();
   // 2. stencil on the owned nodes
-  const double h1 = c.g.h1, h2 = c.g.h2;
-  const double c1 = -1.0 / h1, c2 = -1.0 / h2;
-  const double ih1 = 1.0 / h1, ih2 = 1.0 / h2;
+  const StencilConsts K = make_stencil_consts(c.g);
   double acc = 0.0;
   const int col = threadIdx.x % kTileY + 1;
   for (int row = threadIdx.x / kTileY + 1; row <= t.cx; row += blockDim.x / kTileY) {
@@ -80,14 +114,7 @@ __device__ __forceinline__ double phase_ab_tile(const RankCtx& c, int tile, doub
     const double pc = s[0], pim = s[-kSmemPitch], pip = s[kSmemPitch], pjm = s[-1], pjp = s[1];
     const double a_c = __ldg(&c.a[g]), a_ip = __ldg(&c.a[g + S]);
     const double b_c = __ldg(&c.b[g]), b_jp = __ldg(&c.b[g + 1]);
-    double v;
-    if (EXACT) {
-      v = stencil_literal(pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp, h1, h2, c1, c2);
-    } else {
-      const double ax = c1 * ((a_ip * (pip - pc)) * ih1 - (a_c * (pc - pim)) * ih1);
-      const double ay = c2 * ((b_jp * (pjp - pc)) * ih2 - (b_c * (pc - pjm)) * ih2);
-      v = ax + ay;
-    }
+    const double v = stencil_value<DIV>(K, pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp);
     c.Ap[g] = v;
     acc += v * pc;
   }

@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(kThreads) step_dot_zr_kernel(const RankCtx* __
   store_partials<1>(c, v, s_red);
 }
 
-template <bool FUSE_P, bool EXACT>
+template <bool FUSE_P, int DIV>
 __global__ void __launch_bounds__(kThreads) step_stencil_kernel(const RankCtx* __restrict__ ctx) {
   extern __shared__ double s_tile[];
   __shared__ double s_red[64];
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kThreads) step_stencil_kernel(const RankCtx* _
   const double beta = c.ctl->beta;
   double v[1] = {0.0};
   for (int t = blockIdx.x; t < c.tiles_x * c.tiles_y; t += gridDim.x)
-    v[0] += phase_ab_tile<FUSE_P, EXACT>(c, t, beta, c.p[cur], c.p[cur ^ 1], s_tile);
+    v[0] += phase_ab_tile<FUSE_P, DIV>(c, t, beta, c.p[cur], c.p[cur ^ 1], s_tile);
   store_partials<1>(c, v, s_red);
 }
 
@@ -188,20 +188,22 @@ cudaError_t launch_step_dot_zr(const RankCtx* d_ctx, const RankCtx& h, cudaStrea
   step_dot_zr_kernel<<<step_grid(h), kThreads, 0, s>>>(d_ctx);
   return cudaGetLastError();
 }
-cudaError_t launch_step_stencil(const RankCtx* d_ctx, const RankCtx& h, bool fuse_p, bool exact, cudaStream_t s) {
+template <bool FUSE_P>
+static void launch_stencil_div(const RankCtx* d_ctx, int n, size_t sm, int div, cudaStream_t s) {
+  if (div == kDivTrue)
+    step_stencil_kernel<FUSE_P, kDivTrue><<<n, kThreads, sm, s>>>(d_ctx);
+  else if (div == kDivMarkstein)
+    step_stencil_kernel<FUSE_P, kDivMarkstein><<<n, kThreads, sm, s>>>(d_ctx);
+  else
+    step_stencil_kernel<FUSE_P, kDivRecip><<<n, kThreads, sm, s>>>(d_ctx);
+}
+cudaError_t launch_step_stencil(const RankCtx* d_ctx, const RankCtx& h, bool fuse_p, int div, cudaStream_t s) {
   const int n = step_grid(h);
   const size_t sm = sizeof(double) * kSmemTile;
-  if (fuse_p) {
-    if (exact)
-      step_stencil_kernel<true, true><<<n, kThreads, sm, s>>>(d_ctx);
-    else
-      step_stencil_kernel<true, false><<<n, kThreads, sm, s>>>(d_ctx);
-  } else {
-    if (exact)
-      step_stencil_kernel<false, true><<<n, kThreads, sm, s>>>(d_ctx);
-    else
-      step_stencil_kernel<false, false><<<n, kThreads, sm, s>>>(d_ctx);
-  }
+  if (fuse_p)
+    launch_stencil_div<true>(d_ctx, n, sm, div, s);
+  else
+    launch_stencil_div<false>(d_ctx, n, sm, div, s);
   return cudaGetLastError();
 }
 cudaError_t launch_step_update(const RankCtx* d_ctx, const RankCtx& h, bool fuse_p, cudaStream_t s) {

@@ -36,20 +36,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 
-// Bounded wait: a transaction count that never completes (a programming error) traps after ~4 s
-// instead of hanging the device.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
+// Bounded wait: a transaction count that never completes (a programming error) gives up after ~2 s
+// instead of hanging the device; the caller reports PB_STATUS_TMA_TIMEOUT.
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return true;
   unsigned long long t0;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
   unsigned int spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0xfffu) == 0u) {
+    if ((++spins & 0x3ffu) == 0u) {
       unsigned long long now;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
-      if (now - t0 > 4000000000ull) __trap();
+      if (now - t0 > 2000000000ull) return false;
     }
   }
+  return true;
 }
 
 // 2-D tiled tensor load global -> shared; completion is signalled on `bar` (complete_tx::bytes).

@@ -58,6 +58,8 @@ Solver::~Solver() {
   for (auto& e : ev_) cudaEventDestroy(e);
 }
 
+const void* Solver::host_maps(int l) const { return hmaps_ + (size_t)l * 24 * tensor_map_bytes(); }
+
 double* Solver::array(int l, int which) const {
   if (which < 0 || which > 7) throw std::runtime_error("Solver::array: bad index");
   // arena order: r, w, p0, p1, Ap, a, b, D  (r first so that peers find it at a fixed offset)
@@ -129,8 +131,8 @@ void Solver::finalize() {
     hctx_.push_back(c);
   }
   // tensor maps for both tile heights (host-encoded, copied once)
-  std::vector<char> hmaps(tensor_map_bytes() * 24 * nlocal() + 64);
-  char* hm = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(hmaps.data()) + 63) & ~uintptr_t(63));
+  hmaps_store_.assign(tensor_map_bytes() * 24 * nlocal() + 64, 0);
+  char* hm = hmaps_ = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(hmaps_store_.data()) + 63) & ~uintptr_t(63));
   for (int l = 0; l < nlocal(); ++l) {
     char* dst = hm + (size_t)l * 24 * tensor_map_bytes();
     if (!build_tensor_maps(hctx_[l], 32, dst) || !build_tensor_maps(hctx_[l], 16, dst + 12 * tensor_map_bytes()))

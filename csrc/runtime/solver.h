@@ -21,7 +21,7 @@ struct SolveOptions {
   int norm = PB_NORM_WEIGHTED;
   double delta = 1e-6;
   long long max_iter = -1;  // <0: (M-1)(N-1)
-  int exact_div = 1;        // literal fp64 divisions (reference association)
+  int exact_div = 2;        // stencil divisions: 0 reciprocal multiply, 1 true division, 2 Markstein (= 1 bitwise)
   int ctas_per_sm = 0;      // 0 = auto
   int error_report = 1;
   int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages) or 16 (4 stages); 0 = auto
@@ -54,6 +54,7 @@ class Solver {
   char* arena(int l) const { return arenas_[l]; }
   size_t arena_size(int l) const { return arena_bytes(blocks_[l]); }
   double* array(int l, int which) const;  // 0 w, 1 r, 2 p0, 3 p1, 4 Ap, 5 a, 6 b, 7 D
+  const void* host_maps(int l) const;
   Control* control(int l) const { return reinterpret_cast<Control*>(arenas_[l] + kCtlOffset); }
 
   void ipc_handle(int l, void* out64) const;
@@ -90,6 +91,8 @@ class Solver {
   std::vector<void*> opened_ipc_;    // bases obtained from cudaIpcOpenMemHandle (to close)
   std::vector<RankCtx> hctx_;
   RankCtx* dctx_ = nullptr;
+  std::vector<char> hmaps_store_;
+  char* hmaps_ = nullptr;  // host copy of the tensor maps (64-byte aligned inside hmaps_store_)
   char* dmaps_ = nullptr;  // tensor maps, [nlocal][2 variants][12]
   DeviceOptions* pinned_opts_ = nullptr;
   Control* pinned_ctl_ = nullptr;

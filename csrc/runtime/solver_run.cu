@@ -12,7 +12,7 @@ namespace pb {
 
 void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   if (!fabric_complete_) throw std::runtime_error("persistent solve needs every rank's arena (open_peer) first");
-  const bool exact = opt.exact_div != 0;
+  const int exact = opt.exact_div;
   const bool tma = opt.method == kMethodPersistent;
   int per_sm = tma ? 1 : persistent_max_ctas_per_sm(exact);
   if (per_sm < 1) throw std::runtime_error("persistent kernel does not fit on an SM");
@@ -36,7 +36,8 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
 // distributed step-wise runs are driven from Python with a library collective between the launches.
 void Solver::solve_steps(const SolveOptions& opt, cudaStream_t stream) {
   if (nranks() != 1) throw std::runtime_error("step-wise solve from C++ supports a single rank only");
-  const bool fused = opt.method == kMethodStepFused, exact = opt.exact_div != 0;
+  const bool fused = opt.method == kMethodStepFused;
+  const int exact = opt.exact_div;
   const RankCtx& h = hctx_[0];
   const RankCtx* d = dctx_;
   const long long max_iter = pinned_opts_->max_iter;

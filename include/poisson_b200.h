@@ -25,6 +25,7 @@ extern "C" {
 #define PB_STATUS_BREAKDOWN 2 /* |(Ap,p)| < 1e-15 (S4:875) */
 #define PB_STATUS_RUNNING 3
 #define PB_STATUS_WATCHDOG 4 /* a device-side wait timed out; the solve was abandoned */
+#define PB_STATUS_TMA_TIMEOUT 5 /* a TMA pipeline stage never completed (internal error) */
 
 /* Result of a solve.  Timers are seconds; for multi-rank runs the caller takes the max over ranks. */
 typedef struct pb_stats {
@@ -109,7 +110,8 @@ typedef struct pb_solve_options {
   int norm;
   double delta;
   long long max_iter; /* < 0: (M-1)(N-1) as in S4:1006 */
-  int exact_div;      /* 1: literal fp64 divisions; 0: reciprocal multiplications in the stencil */
+  int exact_div;      /* divisions by h1/h2 in the stencil: 1 true IEEE division, 2 Markstein sequence (same bits as
+                         1, three instructions), 0 multiplication by the reciprocal (last-bit differences) */
   int ctas_per_sm;    /* 0 = auto */
   int error_report;   /* 1: compute the error against the analytic solution after the solve */
   int tile_rows;      /* TMA persistent kernel: 32 (2 pipeline stages) or 16 (4 stages); 0 = auto */
@@ -156,6 +158,10 @@ int pb_step_scalars(pb_solver* s, int local_idx, int phase /* 0 init, 1 alpha, 2
 int pb_step_pack_edges(pb_solver* s, int local_idx, void* dev_buf, int stride, void* cuda_stream);
 int pb_step_unpack_edges(pb_solver* s, int local_idx, const void* dev_buf, int stride, void* cuda_stream);
 int pb_step_error_report(pb_solver* s, int local_idx, void* cuda_stream);
+/* unit-test probe: load one TMA box (map index 0..23, see csrc/cuda/persistent_tma.cu) at element coordinates
+ * (x, y) into dev_out; *dev_status = 1 done, 2 timed out */
+int pb_debug_tma_probe(pb_solver* s, int local_idx, int map_index, int mode, int x, int y, unsigned int nbytes, void* dev_out,
+                       void* dev_status, void* cuda_stream);
 int pb_step_read_control(pb_solver* s, int local_idx, int* iter, int* status, double* diff_norm, void* cuda_stream);
 
 #ifdef __cplusplus

@@ -72,14 +72,14 @@ class PoissonSolver:
 
     # ------------------------------------------------------------------------------------------
     def solve(self, norm: str = "weighted", delta: float = 1e-6, max_iter: int | None = None,
-              method: str = "persistent", exact_div: bool = True, **kw) -> dict:
+              method: str = "persistent", div: str = "markstein", **kw) -> dict:
         """Run one solve; returns the report (iterations, status, norms, errors, timers)."""
         mi = -1 if max_iter is None else int(max_iter)
         t0 = time.perf_counter()
         if self.backend in ("fused", "virtual"):
-            res = self._impl.solve(method=method, norm=norm, delta=delta, max_iter=mi, exact_div=exact_div, **kw)
+            res = self._impl.solve(method=method, norm=norm, delta=delta, max_iter=mi, div=div, **kw)
         elif self.backend in ("nccl", "cpu_dist"):
-            res = self._impl.solve(norm=norm, delta=delta, max_iter=mi, exact_div=exact_div)
+            res = self._impl.solve(norm=norm, delta=delta, max_iter=mi, div=div)
         else:
             st = _native.Stats()
             self._w = torch.zeros((self.M + 1, self.N + 1), dtype=torch.float64)

@@ -13,8 +13,9 @@ import torch
 from . import _native
 
 NORMS = {"weighted": 0, "unweighted": 1}
+DIVS = {"recip": 0, "true": 1, "markstein": 2}
 METHODS = {"persistent": 0, "step_fused": 1, "step_classic": 2, "persistent_ldg": 3}
-STATUS = {0: "max_iter", 1: "converged", 2: "breakdown", 3: "running", 4: "watchdog"}
+STATUS = {0: "max_iter", 1: "converged", 2: "breakdown", 3: "running", 4: "watchdog", 5: "tma_timeout"}
 ARRAYS = {"w": 0, "r": 1, "p0": 2, "p1": 3, "Ap": 4, "a": 5, "b": 6, "D": 7}
 
 
@@ -128,11 +129,16 @@ class GpuSolver:
 
     # -- solve ----------------------------------------------------------------------------------
     def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
-              exact_div: bool = True, ctas_per_sm: int = 0, error_report: bool = True, watchdog_s: float = 0.0,
-              tile_rows: int = 0, stream=None) -> dict:
+              exact_div: bool | None = None, ctas_per_sm: int = 0, error_report: bool = True,
+              watchdog_s: float = 0.0, tile_rows: int = 0, div: str = "markstein", stream=None) -> dict:
+        """``div``: how the stencil divides by h1/h2 -- "true" (IEEE division), "markstein" (three-instruction
+        sequence with the same bits, default) or "recip" (multiply by the reciprocal).  ``exact_div`` is the
+        older boolean spelling: True -> "true", False -> "recip"."""
         if not self._finalized:
             self.finalize()
-        opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, int(exact_div), ctas_per_sm,
+        if exact_div is not None:
+            div = "true" if exact_div else "recip"
+        opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, DIVS[div], ctas_per_sm,
                                    int(error_report), tile_rows, watchdog_s)
         st = _native.Stats()
         with torch.cuda.device(self.device):
@@ -141,8 +147,8 @@ class GpuSolver:
         out = st.as_dict()
         out["status_name"] = STATUS.get(st.status, "?")
         out.update(self.info())
-        if st.status == 4:
-            raise RuntimeError("device-side watchdog fired: a rank did not reach a reduction in time")
+        if st.status in (4, 5):
+            raise RuntimeError(f"device-side {STATUS[st.status]}: the solve was abandoned (debug: {out})")
         return out
 
     def solution_host(self) -> torch.Tensor:
@@ -159,6 +165,18 @@ class GpuSolver:
         _native.check(self.lib.pb_solver_gather_block(self._h, local_idx, out.data_ptr(), blk.ny, _stream_ptr(None)),
                       "pb_solver_gather_block")
         return out
+
+    def tma_probe(self, map_index: int, x: int, y: int, box_cols: int, box_rows: int, local_idx: int = 0,
+                  mode: int = 0):
+        """Unit-test hook: one TMA box load; returns ``(status, box)`` with ``box`` of shape (box_rows, box_cols)."""
+        dev = f"cuda:{self.device}"
+        out = torch.full((box_rows, box_cols), float("nan"), dtype=torch.float64, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        _native.check(self.lib.pb_debug_tma_probe(self._h, local_idx, map_index, mode, x, y, box_rows * box_cols * 8,
+                                                  out.data_ptr(), status.data_ptr(), _stream_ptr(None)),
+                      "pb_debug_tma_probe")
+        torch.cuda.synchronize()
+        return int(status.item()), out
 
     # -- kernel-level step API ------------------------------------------------------------------
     def step(self, name: str, *args, local_idx: int = 0, stream=None):

@@ -67,11 +67,11 @@ class CollectiveSolver:
 
     # ------------------------------------------------------------------------------------------
     def solve(self, norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1, check_every: int = 16,
-              exact_div: bool = True) -> dict:
+              div: str = "markstein") -> dict:
         if max_iter < 0:
             max_iter = (self.M - 1) * (self.N - 1)
         if self.kind == "cuda":
-            res = self._solve_cuda(norm, delta, max_iter, check_every, exact_div)
+            res = self._solve_cuda(norm, delta, max_iter, check_every, div)
             return combine_reports(res, self.M, self.N, device=f"cuda:{self.gpu.device}")
         res = self._solve_cpu(norm, delta, max_iter)
         return combine_reports(res, self.M, self.N, device="cpu")
@@ -93,8 +93,8 @@ class CollectiveSolver:
         if self.world > 1:
             dist.all_reduce(self.red[:2])
 
-    def _solve_cuda(self, norm, delta, max_iter, check_every, exact_div):
-        from ..ops.gpu import NORMS
+    def _solve_cuda(self, norm, delta, max_iter, check_every, div):
+        from ..ops.gpu import DIVS, NORMS
 
         g = self.gpu
         ev0, ev1, ev2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
@@ -114,7 +114,7 @@ class CollectiveSolver:
             for _ in range(min(check_every, max_iter - k)):
                 g.step("update_p")
                 self._halo_cuda()
-                g.step("stencil", 0, int(exact_div))
+                g.step("stencil", 0, DIVS[div])
                 g.step("reduce_local", 1)
                 self._allreduce_cuda()
                 g.step("scalars", 1)

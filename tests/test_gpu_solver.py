@@ -101,11 +101,26 @@ def test_virtual_ranks_ldg_kernel(pg):
     s.close()
 
 
-def test_reciprocal_stencil_keeps_iteration_count():
+@pytest.mark.parametrize("div", ["true", "recip", "markstein"])
+def test_division_modes_keep_iteration_count(div):
     for grid in [(40, 40), (400, 600)]:
         s = _solver(*grid)
-        res = s.solve(exact_div=False)
+        res = s.solve(div=div)
         assert res["iters"] == ITERS_WEIGHTED[grid]
+        s.close()
+
+
+@pytest.mark.parametrize("method", ["persistent", "step_fused"])
+def test_markstein_division_is_bit_identical_to_true_division(method):
+    """q' = fma(fma(-q, h, x), y, q), y = RN(1/h), must reproduce x / h exactly: the whole solution agrees bitwise."""
+    for grid in [(80, 80), (400, 600), (333, 517)]:
+        s = _solver(*grid)
+        ra = s.solve(method=method, div="true")
+        wa = s.solution_host().clone()
+        rb = s.solve(method=method, div="markstein")
+        wb = s.solution_host()
+        assert ra["iters"] == rb["iters"]
+        assert torch.equal(wa, wb)
         s.close()
 
 
