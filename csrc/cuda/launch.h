@@ -47,4 +47,8 @@ cudaError_t launch_pack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, double
 cudaError_t launch_unpack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, const double* recvbuf, int stride,
                                 cudaStream_t stream);
 
+// unit test of the division sequences (step_kernels.cu)
+cudaError_t launch_div_check(double h, unsigned long long n, unsigned long long seed, unsigned long long* counts,
+                             cudaStream_t stream);
+
 }  // namespace pb

@@ -213,7 +213,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         if (col < 0 || col >= cy + 2) continue;
         const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
         if (!(row_in || col_in)) continue;
-        const double v = safe_div(s_r[e], s_D[e]) + beta * s_p[e];
+        const double v = fma(beta, s_p[e], safe_div(s_r[e], s_D[e]));
         s_p[e] = v;
         const int li = li0 - 1 + row, lj = lj0 - 1 + col;
         const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
@@ -231,7 +231,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
             const double b_c = s_b[(row - 1) * BC + (col - 1)], b_jp = s_b[(row - 1) * BC + col];
             const double v = stencil_value<DIV>(K, pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp);
             c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
-            acc_ab += v * pc;
+            acc_ab = fma(v, pc, acc_ab);
           }
         }
       }
@@ -282,13 +282,13 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           const int li = li0 + row, lj = lj0 + col;
           const size_t g = (size_t)li * S_pitch + (lj + kColOff);
           const double w_old = s_w[e];
-          const double w_new = w_old + alpha * s_p[e];
-          const double r_new = s_r[e] - alpha * s_Ap[e];
+          const double w_new = fma(alpha, s_p[e], w_old);
+          const double r_new = fma(-alpha, s_Ap[e], s_r[e]);
           c.w[g] = w_new;
           c.r[g] = r_new;
-          const double d = w_new - w_old;
-          acc_d += d * d;
-          acc_zr += safe_div(r_new, s_D[e]) * r_new;
+          const double d = __dsub_rn(w_new, w_old);
+          acc_d = fma(d, d, acc_d);
+          acc_zr = fma(safe_div(r_new, s_D[e]), r_new, acc_zr);
           if (li == 1 && c.nbr_r[kXm])
             c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
           if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kThreads) step_update_p_kernel(const RankCtx* 
     if (col > t.cy) continue;
     for (int row = threadIdx.x / kTileY + 1; row <= t.cx; row += blockDim.x / kTileY) {
       const size_t g = (size_t)(t.li0 - 1 + row) * c.pitch + (t.lj0 - 1 + col + kColOff);
-      p[g] = safe_div(c.r[g], c.D[g]) + beta * p[g];
+      p[g] = fma(beta, p[g], safe_div(c.r[g], c.D[g]));
     }
   }
 }
@@ -172,6 +172,36 @@ __global__ void unpack_edges_kernel(const RankCtx* __restrict__ ctx, const doubl
     if (c.nbr[kYm] >= 0) p[(size_t)(t + 1) * c.pitch + (0 + kColOff)] = buf[2 * stride + t];
     if (c.nbr[kYp] >= 0) p[(size_t)(t + 1) * c.pitch + (c.ny + 1 + kColOff)] = buf[3 * stride + t];
   }
+}
+
+// Debug / unit test: how often do the cheap division sequences differ from x / h in the last bit?
+// counts[0] = samples, [1] = one-correction mismatches, [2] = two-correction mismatches, [3] = x*y mismatches.
+__global__ void div_check_kernel(double h, unsigned long long n, unsigned long long seed, unsigned long long* counts) {
+  const double y = 1.0 / h;
+  unsigned long long bad1 = 0, bad2 = 0, bad0 = 0, cnt = 0;
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    unsigned long long s = (i + seed) * 6364136223846793005ull + 1442695040888963407ull;
+    s ^= s >> 29;
+    s *= 0xbf58476d1ce4e5b9ull;
+    s ^= s >> 32;
+    // mantissa random, exponent in [-40, 40], random sign
+    const double m = 1.0 + (double)(s >> 12) * (1.0 / 4503599627370496.0);
+    const int e = (int)((s >> 3) % 81) - 40;
+    const double x = ((s & 1) ? -1.0 : 1.0) * scalbn(m, e);
+    const double t = x / h;
+    const double q0 = x * y;
+    const double q1 = fma(fma(-q0, h, x), y, q0);
+    const double q2 = fma(fma(-q1, h, x), y, q1);
+    bad0 += (q0 != t), bad1 += (q1 != t), bad2 += (q2 != t), ++cnt;
+  }
+  atomicAdd(&counts[0], cnt), atomicAdd(&counts[1], bad1), atomicAdd(&counts[2], bad2), atomicAdd(&counts[3], bad0);
+}
+
+cudaError_t launch_div_check(double h, unsigned long long n, unsigned long long seed, unsigned long long* counts,
+                             cudaStream_t s) {
+  div_check_kernel<<<592, 256, 0, s>>>(h, n, seed, counts);
+  return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -158,6 +158,9 @@ int pb_step_scalars(pb_solver* s, int local_idx, int phase /* 0 init, 1 alpha, 2
 int pb_step_pack_edges(pb_solver* s, int local_idx, void* dev_buf, int stride, void* cuda_stream);
 int pb_step_unpack_edges(pb_solver* s, int local_idx, const void* dev_buf, int stride, void* cuda_stream);
 int pb_step_error_report(pb_solver* s, int local_idx, void* cuda_stream);
+/* unit test: compares x*y, one- and two-correction Markstein quotients with x / h on n pseudo-random x;
+ * dev_counts = u64[4] {samples, one-correction mismatches, two-correction mismatches, x*y mismatches} */
+int pb_debug_div_check(double h, unsigned long long n, unsigned long long seed, void* dev_counts, void* cuda_stream);
 /* unit-test probe: load one TMA box (map index 0..23, see csrc/cuda/persistent_tma.cu) at element coordinates
  * (x, y) into dev_out; *dev_status = 1 done, 2 timed out */
 int pb_debug_tma_probe(pb_solver* s, int local_idx, int map_index, int mode, int x, int y, unsigned int nbytes, void* dev_out,
