@@ -208,6 +208,9 @@ int pb_step_unpack_edges(pb_solver* s, int l, const void* buf, int stride, void*
 int pb_step_error_report(pb_solver* s, int l, void* st) {
   PB_STEP(pb::launch_error_report(s->impl.device_ctx(l), s->impl.host_ctx(l), as_stream(st)));
 }
+int pb_solver_xgpu_bench(pb_solver* s, int iters, int mode, int edge, int ctas, void* st, double* out2) {
+  return guarded([&] { s->impl.xgpu_bench(iters, mode, edge, ctas, as_stream(st), out2); });
+}
 int pb_debug_div_check(double h, unsigned long long n, unsigned long long seed, void* counts, void* st) {
   return guarded([&] { PB_CUDA_CHECK(pb::launch_div_check(h, n, seed, static_cast<unsigned long long*>(counts), as_stream(st))); });
 }

@@ -14,6 +14,9 @@ cudaError_t launch_error_report(const RankCtx* d_ctx, const RankCtx& h_ctx, cuda
 cudaError_t launch_gather_interior(const double* w, int nx, int ny, int pitch, double* out, long long ld,
                                    cudaStream_t stream);
 
+// communication micro-benchmark (persistent.cu): reductions alone (mode 0) or halo stores + reduction (mode 1)
+cudaError_t launch_xgpu_bench(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int iters, int mode, int edge,
+                              cudaStream_t stream);
 // `div` everywhere: 0 reciprocal multiply, 1 true division, 2 Markstein (bit-identical to 1), see phases.cuh
 // KP (persistent.cu)
 size_t persistent_smem_bytes();

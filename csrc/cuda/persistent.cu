@@ -155,6 +155,62 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
 #undef PB_STAMP
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Micro-benchmark of the communication primitives alone (BASELINE.json config 5): `iters` rounds of
+//   mode 0: cross-rank reduction of two doubles, no halo traffic
+//   mode 1: every rank stores `edge` doubles into each neighbour's r ring (spread over all CTAs), then
+//           the reduction whose release/acquire chain publishes them -- i.e. one complete halo exchange
+// CTA 0 of each rank measures the whole loop with %globaltimer -> Control::t_total (ns).
+__global__ void __launch_bounds__(kThreads, 1)
+xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters, int mode, int edge) {
+  __shared__ RankCtx c;
+  __shared__ double s_red[80];
+  const int vrank = blockIdx.x / ctas_per_rank;
+  const int cta = blockIdx.x - vrank * ctas_per_rank, ncta = ctas_per_rank;
+  {
+    const int* src = reinterpret_cast<const int*>(ctxs + vrank);
+    int* dst = reinterpret_cast<int*>(&c);
+    for (int i = threadIdx.x; i < (int)(sizeof(RankCtx) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  unsigned int seq = c.ctl->red_seq, arrive_target = 0;
+  const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
+  double check = 0.0;
+  bool ok = true;
+  const unsigned long long t0 = globaltimer_ns();
+  for (int it = 0; it < iters && ok; ++it) {
+    if (mode == 1) {
+      const int gtid = cta * kThreads + threadIdx.x, gsz = ncta * kThreads;
+      const double val = (double)(it + 1);
+      for (int i = gtid; i < edge; i += gsz) {
+        if (c.nbr_r[kXm] && i < c.ny) c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (i + 1 + kColOff)] = val;
+        if (c.nbr_r[kXp] && i < c.ny) c.nbr_r[kXp][(size_t)(i + 1 + kColOff)] = val;
+        if (c.nbr_r[kYm] && i < c.nx) c.nbr_r[kYm][(size_t)(i + 1) * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = val;
+        if (c.nbr_r[kYp] && i < c.nx) c.nbr_r[kYp][(size_t)(i + 1) * c.nbr_pitch[kYp] + kColOff] = val;
+      }
+    }
+    double v[2] = {threadIdx.x == 0 ? 1.0 : 0.0, 0.0};
+    ++seq;
+    arrive_target += ncta;
+    const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr);
+    ok = rr.ok;
+    check += rr.v[0];
+  }
+  if (cta == 0 && threadIdx.x == 0) {
+    c.ctl->t_total = globaltimer_ns() - t0;
+    c.ctl->red_seq = seq;
+    c.ctl->red[0] = check;  // = iters * nranks * ncta when every reduction was complete
+    c.ctl->status = ok ? PB_STATUS_CONVERGED : PB_STATUS_WATCHDOG;
+  }
+}
+
+cudaError_t launch_xgpu_bench(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int iters, int mode, int edge,
+                              cudaStream_t stream) {
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&iters, (void*)&mode, (void*)&edge};
+  return cudaLaunchCooperativeKernel((const void*)xgpu_bench_kernel, dim3(nvirt * ctas_per_rank), dim3(kThreads), args,
+                                     0, stream);
+}
+
 size_t persistent_smem_bytes() { return sizeof(double) * kSmemTile; }
 
 static const void* persistent_fn(int div) {

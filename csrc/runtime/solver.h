@@ -66,6 +66,8 @@ class Solver {
   // the two halves of solve(): enqueue everything without host synchronisation / wait and read the report
   void enqueue(const SolveOptions& opt, cudaStream_t stream);
   void collect(cudaStream_t stream, pb_stats* out);
+  // communication micro-benchmark: returns {ns per round (this rank), checksum}; collective over all ranks
+  void xgpu_bench(int iters, int mode, int edge, int ctas, cudaStream_t stream, double out[2]);
   // dense (M+1) x (N+1) host field from the local ranks' blocks (other ranks' nodes are left untouched)
   void copy_solution_to_host(double* full, cudaStream_t stream);
   // dense nx x ny device copy of one local block's owned nodes

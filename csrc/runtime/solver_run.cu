@@ -152,6 +152,20 @@ void Solver::solve(const SolveOptions& opt, cudaStream_t stream, pb_stats* out) 
   collect(stream, out);
 }
 
+void Solver::xgpu_bench(int iters, int mode, int edge, int ctas, cudaStream_t stream, double out[2]) {
+  if (!fabric_complete_) throw std::runtime_error("xgpu_bench needs every rank's arena");
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  if (ctas <= 0) ctas = sm_count_ / nlocal();
+  ctas = std::min(ctas, kMaxCtas);
+  for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
+  PB_CUDA_CHECK(launch_xgpu_bench(dctx_, nlocal(), ctas, iters, mode, edge, stream));
+  PB_CUDA_CHECK(cudaMemcpyAsync(pinned_ctl_, control(0), sizeof(Control), cudaMemcpyDeviceToHost, stream));
+  PB_CUDA_CHECK(cudaStreamSynchronize(stream));
+  if (pinned_ctl_[0].status == PB_STATUS_WATCHDOG) throw std::runtime_error("xgpu_bench: watchdog fired");
+  out[0] = (double)pinned_ctl_[0].t_total / (double)std::max(1, iters);
+  out[1] = pinned_ctl_[0].red[0];
+}
+
 void Solver::gather_block(int l, double* dev_out, long long ld, cudaStream_t stream) {
   const LocalBlock& b = blocks_[l];
   PB_CUDA_CHECK(launch_gather_interior(array(l, 0), b.nx, b.ny, b.pitch, dev_out, ld, stream));

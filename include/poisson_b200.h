@@ -158,6 +158,10 @@ int pb_step_scalars(pb_solver* s, int local_idx, int phase /* 0 init, 1 alpha, 2
 int pb_step_pack_edges(pb_solver* s, int local_idx, void* dev_buf, int stride, void* cuda_stream);
 int pb_step_unpack_edges(pb_solver* s, int local_idx, const void* dev_buf, int stride, void* cuda_stream);
 int pb_step_error_report(pb_solver* s, int local_idx, void* cuda_stream);
+/* communication micro-benchmark (collective over all ranks): `iters` rounds of the in-kernel cross-rank
+ * reduction (mode 0) or of halo stores of `edge` doubles per neighbour + reduction (mode 1);
+ * out2 = {ns per round measured on this rank, checksum}.  ctas = 0: one CTA per SM. */
+int pb_solver_xgpu_bench(pb_solver* s, int iters, int mode, int edge, int ctas, void* cuda_stream, double* out2);
 /* unit test: compares x*y, one- and two-correction Markstein quotients with x / h on n pseudo-random x;
  * dev_counts = u64[4] {samples, one-correction mismatches, two-correction mismatches, x*y mismatches} */
 int pb_debug_div_check(double h, unsigned long long n, unsigned long long seed, void* dev_counts, void* cuda_stream);

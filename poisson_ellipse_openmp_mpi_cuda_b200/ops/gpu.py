@@ -166,6 +166,13 @@ class GpuSolver:
                       "pb_solver_gather_block")
         return out
 
+    def xgpu_bench(self, iters: int, mode: int = 0, edge: int = 0, ctas: int = 0) -> tuple[float, float]:
+        """Communication micro-benchmark (collective): ns per round on this rank, checksum."""
+        out = (C.c_double * 2)()
+        _native.check(self.lib.pb_solver_xgpu_bench(self._h, iters, mode, edge, ctas, _stream_ptr(None), out),
+                      "pb_solver_xgpu_bench")
+        return out[0], out[1]
+
     def tma_probe(self, map_index: int, x: int, y: int, box_cols: int, box_rows: int, local_idx: int = 0,
                   mode: int = 0):
         """Unit-test hook: one TMA box load; returns ``(status, box)`` with ``box`` of shape (box_rows, box_cols)."""
