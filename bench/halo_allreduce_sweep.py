@@ -45,7 +45,11 @@ def main():
     for edge in (64, 256, 1024, 4096, 16384):
         fs.solver.xgpu_bench(20, 1, edge)
         ns, _ = fs.solver.xgpu_bench(iters, 1, edge)
-        rows.append({"what": "halo_exchange", "edge_doubles": edge, "impl": "ours_peer_store+reduction",
+        rows.append({"what": "halo_exchange", "edge_doubles": edge, "impl": "ours_peer_store+sys_fenced_reduction",
+                     "us": max_over_ranks(ns, dev) / 1e3, "neighbours": len(nbrs)})
+        fs.solver.xgpu_bench(20, 2, edge)
+        ns, _ = fs.solver.xgpu_bench(iters, 2, edge)
+        rows.append({"what": "halo_exchange", "edge_doubles": edge, "impl": "ours_peer_store+counter+reduction",
                      "us": max_over_ranks(ns, dev) / 1e3, "neighbours": len(nbrs)})
     if world > 1:
         x = torch.ones(2, dtype=torch.float64, device=dev)

@@ -26,6 +26,7 @@ constexpr int kSlotWords = 4;       // 2 doubles -> 4 (payload32 | seq32) words
 constexpr size_t kCtlOffset = 0;                   // Control
 constexpr size_t kSlotsOffset = 4096;              // [2 parities][kMaxRanks][kSlotWords] u64
 constexpr size_t kArriveOffset = 8192;             // arrival counter (u32) + padding
+constexpr size_t kHaloCntOffset = 8192 + 1024;     // u64[4]: halo tiles received per direction (monotonic)
 constexpr int kPartialStride = 8;                  // doubles per CTA in the partials area
 constexpr size_t kPartialsOffset = 16384;          // [kMaxCtas][kPartialStride] doubles
 constexpr size_t kHeaderBytes = 131072;            // arrays start here; r is the first array
@@ -70,6 +71,10 @@ struct RankCtx {
   unsigned long long* slots;
   unsigned long long* peer_slots[kMaxRanks];
   Control* ctl;
+  // halo completion counters: ours (incremented by the neighbours) and, per direction, the neighbour's
+  // counter that our stores into its ring must bump (its opposite direction)
+  unsigned long long* halo_cnt;
+  unsigned long long* nbr_halo_cnt[4];
   const void* tmaps;  // CUtensorMap[2][12] in device memory (TMA persistent kernel), see persistent_tma.cu
   int sys_scope;  // 1: some peer lives on another device, fences must be system-wide
   // tiling of the block for the stencil phase

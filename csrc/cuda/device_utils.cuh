@@ -42,6 +42,14 @@ __device__ __forceinline__ int ld_relaxed_gpu_s32(const int* p) {
   asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_add_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 // Orders earlier generic-proxy accesses (ours, or ones we acquired from other SMs / GPUs) before later
@@ -87,10 +95,13 @@ constexpr unsigned long long kDefaultWatchdogNs = 20ull * 1000ull * 1000ull * 10
 // [cta_lo, cta_lo + ncta) of a rank, the same number of times on every rank.  `seq` is the 1-based
 // sequence number of this reduction (persisting across launches through Control::red_seq), `cta` the
 // CTA index inside the rank.  `smem` provides 64 + 8 doubles of scratch.
+// `sys_fences`: the reduction also publishes halo values that were written with plain stores into peer
+// memory (system-scope release/acquire around the records).  Kernels that track halo completion with their
+// own counters pass false and keep every fence of the reduction at GPU scope.
 template <int NV>
 __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&val)[NV], unsigned int seq,
                                                     unsigned int arrive_target, int cta, int ncta,
-                                                    double* smem, bool did_peer_stores) {
+                                                    double* smem, bool did_peer_stores, bool sys_fences) {
   static_assert(NV <= kRedValues, "too many values");
   __shared__ int s_last;
   block_sum<NV>(val, smem);
@@ -98,7 +109,7 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
 #pragma unroll
     for (int k = 0; k < NV; ++k) c.partials[cta * kPartialStride + k] = val[k];
     // release: partials (and any halo values this CTA stored into a neighbour GPU) before the arrival
-    if (did_peer_stores && c.sys_scope)
+    if (did_peer_stores && sys_fences)
       fence_acq_rel_sys();
     else
       fence_acq_rel_gpu();
@@ -134,7 +145,7 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
       }
       const size_t off = ((size_t)(seq & 1u) * kMaxRanks + (size_t)c.rank) * kSlotWords;
       unsigned long long* dst = c.peer_slots[threadIdx.x] + off;
-      if (c.sys_scope)
+      if (sys_fences)
         fence_acq_rel_sys();  // release (cumulative over the halo stores acquired through the arrivals)
       else
         fence_acq_rel_gpu();
@@ -181,7 +192,7 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
         mine[k] = __longlong_as_double((long long)bits);
       }
     }
-    if (c.sys_scope)
+    if (sys_fences)
       fence_acq_rel_sys();  // acquire: halo values stored by neighbours before their arrival
     else
       fence_acq_rel_gpu();

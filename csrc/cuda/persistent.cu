@@ -69,7 +69,7 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
     for (int t = cta; t < ntiles; t += ncta) v[0] += dot_zr_tile(c, t);
     ++seq;
     arrive_target += ncta;
-    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, c.sys_scope != 0);
     if (!rr.ok) {
       if (threadIdx.x == 0 && cta == 0) {
         ctl->status = PB_STATUS_WATCHDOG;
@@ -95,7 +95,7 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
       PB_STAMP(t_ab);
       ++seq;
       arrive_target += ncta;
-      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, c.sys_scope != 0);
       PB_STAMP(t_r1);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -116,7 +116,7 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
       PB_STAMP(t_c);
       ++seq;
       arrive_target += ncta;
-      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, has_nbr);
+      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, has_nbr, c.sys_scope != 0);
       PB_STAMP(t_r2);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -159,7 +159,10 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
 // Micro-benchmark of the communication primitives alone (BASELINE.json config 5): `iters` rounds of
 //   mode 0: cross-rank reduction of two doubles, no halo traffic
 //   mode 1: every rank stores `edge` doubles into each neighbour's r ring (spread over all CTAs), then
-//           the reduction whose release/acquire chain publishes them -- i.e. one complete halo exchange
+//           the reduction whose system-scope release/acquire chain publishes them (protocol of persistent.cu)
+//   mode 2: the first CTAs store the edges, release them with one system fence each and bump the
+//           neighbour's halo counter; the reduction stays at GPU scope; CTA 0 finally checks its own
+//           counters (protocol of persistent_tma.cu)
 // CTA 0 of each rank measures the whole loop with %globaltimer -> Control::t_total (ns).
 __global__ void __launch_bounds__(kThreads, 1)
 xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters, int mode, int edge) {
@@ -177,8 +180,27 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
   double check = 0.0;
   bool ok = true;
+  const int npush = min(ncta, 16);  // mode 2: CTAs that act as "perimeter" CTAs
+  unsigned long long base[4];
+  for (int d = 0; d < 4; ++d) base[d] = ld_relaxed_sys_u64(c.halo_cnt + d);
   const unsigned long long t0 = globaltimer_ns();
   for (int it = 0; it < iters && ok; ++it) {
+    if (mode == 2 && cta < npush) {
+      const int gtid = cta * kThreads + threadIdx.x, gsz = npush * kThreads;
+      const double val = (double)(it + 1);
+      for (int i = gtid; i < edge; i += gsz) {
+        if (c.nbr_r[kXm] && i < c.ny) c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (i + 1 + kColOff)] = val;
+        if (c.nbr_r[kXp] && i < c.ny) c.nbr_r[kXp][(size_t)(i + 1 + kColOff)] = val;
+        if (c.nbr_r[kYm] && i < c.nx) c.nbr_r[kYm][(size_t)(i + 1) * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = val;
+        if (c.nbr_r[kYp] && i < c.nx) c.nbr_r[kYp][(size_t)(i + 1) * c.nbr_pitch[kYp] + kColOff] = val;
+      }
+      __syncthreads();
+      if (threadIdx.x == 32 && has_nbr) {
+        fence_acq_rel_sys();
+        for (int d = 0; d < 4; ++d)
+          if (c.nbr_r[d]) red_add_relaxed_sys_u64(c.nbr_halo_cnt[d], 1ull);
+      }
+    }
     if (mode == 1) {
       const int gtid = cta * kThreads + threadIdx.x, gsz = ncta * kThreads;
       const double val = (double)(it + 1);
@@ -192,9 +214,19 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     double v[2] = {threadIdx.x == 0 ? 1.0 : 0.0, 0.0};
     ++seq;
     arrive_target += ncta;
-    const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr);
+    const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr, mode == 1 && c.sys_scope != 0);
     ok = rr.ok;
     check += rr.v[0];
+    if (mode == 2 && cta == 0 && threadIdx.x == 0) {
+      for (int d = 0; d < 4; ++d) {
+        if (!c.nbr_r[d]) continue;
+        // every rank has the same number of pushing CTAs, so each neighbour adds npush per round
+        const unsigned long long want = base[d] + (unsigned long long)(it + 1) * (unsigned long long)npush;
+        unsigned long long spins = 0;
+        while (ld_acquire_sys_u64(c.halo_cnt + d) < want && ++spins < (1ull << 26)) {
+        }
+      }
+    }
   }
   if (cta == 0 && threadIdx.x == 0) {
     c.ctl->t_total = globaltimer_ns() - t0;

@@ -67,9 +67,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * 12;
 
   Control* ctl = c.ctl;
-  const int tiles_y = (c.ny + TY - 1) / TY;
-  const int ntiles = ((c.nx + TX - 1) / TX) * tiles_y;
+  const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + TX - 1) / TX;
+  const int ntiles = tiles_x * tiles_y;
   const int nmine = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
+  // Tiles are enumerated perimeter first: a CTA stores its halo values (phase C) and needs its neighbours'
+  // (phase AB) at the start of a phase, so the system-scope release of the stores and the NVLink latency are
+  // hidden behind the interior tiles instead of sitting in front of a reduction.
+  const bool thin = tiles_x <= 2 || tiles_y <= 2;
+  const int n_perim = thin ? ntiles : 2 * tiles_y + 2 * (tiles_x - 2);
+  const int n_my_perim = cta < n_perim ? (n_perim - cta + ncta - 1) / ncta : 0;  // my tiles j < n_my_perim
   const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
   const bool timing = (cta == 0 && threadIdx.x == 0);
@@ -86,13 +92,58 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 
   auto tile_origin = [&](int j, int& li0, int& lj0) {
     const int t = cta + j * ncta;
-    const int tx = t / tiles_y, ty = t - tx * tiles_y;
+    int tx, ty;
+    if (thin) {
+      tx = t / tiles_y, ty = t - tx * tiles_y;
+    } else if (t < tiles_y) {
+      tx = 0, ty = t;
+    } else if (t < 2 * tiles_y) {
+      tx = tiles_x - 1, ty = t - tiles_y;
+    } else if (t < 2 * tiles_y + (tiles_x - 2)) {
+      tx = 1 + t - 2 * tiles_y, ty = 0;
+    } else if (t < n_perim) {
+      tx = 1 + t - 2 * tiles_y - (tiles_x - 2), ty = tiles_y - 1;
+    } else {
+      const int q = t - n_perim;
+      tx = 1 + q / (tiles_y - 2), ty = 1 + q % (tiles_y - 2);
+    }
     li0 = 1 + tx * TX;
     lj0 = 1 + ty * TY;
   };
+  // Halo completion counters (see ctx.h): value at launch, and by how much one phase C of the neighbour
+  // raises ours (= the number of its tiles along the shared edge).
+  unsigned long long halo_base[4];
+  int edge_tiles[4];
+#pragma unroll
+  for (int d = 0; d < 4; ++d) {
+    halo_base[d] = ld_relaxed_sys_u64(c.halo_cnt + d);
+    edge_tiles[d] = c.nbr_r[d] ? (d < 2 ? (c.nbr_ny[d] + TY - 1) / TY : (c.nbr_nx[d] + TX - 1) / TX) : 0;
+  }
+  // thread 0: wait until the ring cells of the tile at (li0, lj0) hold the neighbours' r of round `rounds`
+  auto wait_halo = [&](int li0, int lj0, long long rounds) {
+    const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+    const bool touch[4] = {li0 == 1, li0 + cx - 1 == c.nx, lj0 == 1, lj0 + cy - 1 == c.ny};
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      if (!touch[d] || !c.nbr_r[d]) continue;
+      const unsigned long long want = halo_base[d] + (unsigned long long)rounds * (unsigned long long)edge_tiles[d];
+      unsigned long long t0 = 0;
+      unsigned int spins = 0;
+      while (ld_acquire_sys_u64(c.halo_cnt + d) < want) {
+        if ((++spins & 0xffu) == 0u) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          if (now - t0 > (ctl->watchdog_ns ? ctl->watchdog_ns : kDefaultWatchdogNs)) {
+            ctl->red[2] = 1.0;  // sticky marker (zeroed by the host before the launch): halo wait timed out
+            break;
+          }
+        }
+      }
+    }
+  };
   // Phase-AB loads of tile j into stage `st`.  part 1 = everything that does not depend on the other CTAs'
   // phase C (D, p, a, b; arms the barrier with the full byte count), part 2 = the r box.
-  auto issue_ab_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2) {
+  auto issue_ab_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2, long long rounds) {
     if (threadIdx.x == 0) {
       int li0, lj0;
       tile_origin(j, li0, lj0);
@@ -107,11 +158,17 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         tma_load_2d(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 2, y + 1, bar);
         tma_load_2d(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 2, y + 1, bar);
       }
-      if (part2) tma_load_2d(sb, maps + kMapRExt, x, y, bar);
+      if (part2) {
+        if (has_nbr) {
+          wait_halo(li0, lj0, rounds);
+          fence_proxy_async();  // the neighbours' generic-proxy stores, just acquired -> TMA read
+        }
+        tma_load_2d(sb, maps + kMapRExt, x, y, bar);
+      }
     }
   };
-  auto issue_ab = [&](int j, int pbuf) {
-    issue_ab_part(j, n_issued % S, pbuf, true, true);
+  auto issue_ab = [&](int j, int pbuf, long long rounds) {
+    issue_ab_part(j, n_issued % S, pbuf, true, true, rounds);
     ++n_issued;
   };
   auto issue_c = [&](int j, int pbuf) {
@@ -165,7 +222,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   int cur = 0;
   // Prefetch for the first phase AB.  Everything it reads was written by the assembly kernel (an earlier
   // launch), so both parts can go out before the initial reduction.
-  for (int j = 0; j < npre; ++j) issue_ab(j, cur);
+  for (int j = 0; j < npre; ++j) issue_ab(j, cur, 0);
 
   // ---- init: zr_old = (D^-1 r, r); plain loads, executed once ----
   double zr_old;
@@ -175,7 +232,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     for (int t = cta; t < nt32; t += ncta) v[0] += dot_zr_tile(c, t);
     ++seq;
     arrive_target += ncta;
-    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
     if (!rr.ok) {
       drain();
       if (threadIdx.x == 0 && cta == 0) {
@@ -196,7 +253,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     // ======================= phase AB (tiles 0..npre-1 are already in flight) =======================
     double acc_ab = 0.0;
     for (int j = 0; j < nmine && tma_ok; ++j) {
-      if (j + S - 1 < nmine) issue_ab(j + S - 1, cur);
+      if (j + S - 1 < nmine) issue_ab(j + S - 1, cur, k - 1);
       unsigned char* sb = wait_stage();
       if (!tma_ok) break;
       const double* s_r = reinterpret_cast<const double*>(sb);
@@ -248,7 +305,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       double v[1] = {acc_ab};
       ++seq;
       arrive_target += ncta;
-      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false);
+      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
       PB_STAMP(t_r1);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -263,6 +320,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     alpha = zr_old / denom;
     // ======================= phase C =======================
     double acc_d = 0.0, acc_zr = 0.0;
+    int pushed[4] = {0, 0, 0, 0};  // tiles of this CTA whose edge values went into each neighbour's ring
     for (int j = 0; j < nmine && tma_ok; ++j) {
       if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
       unsigned char* sb = wait_stage();
@@ -297,7 +355,18 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
         }
       }
-      __syncthreads();  // stage free
+      if (has_nbr && j < n_my_perim) {
+        pushed[kXm] += (li0 == 1), pushed[kXp] += (li0 + cx - 1 == c.nx);
+        pushed[kYm] += (lj0 == 1), pushed[kYp] += (lj0 + cy - 1 == c.ny);
+      }
+      __syncthreads();  // stage free; all halo stores of this tile are issued
+      if (has_nbr && j == n_my_perim - 1 && threadIdx.x == 32) {
+        // release the halo stores of all perimeter tiles of this CTA system-wide, then count them in
+        fence_acq_rel_sys();
+#pragma unroll
+        for (int d = 0; d < 4; ++d)
+          if (pushed[d] && c.nbr_r[d]) red_add_relaxed_sys_u64(c.nbr_halo_cnt[d], (unsigned long long)pushed[d]);
+      }
       ++n_consumed;
     }
     if (!tma_ok) break;
@@ -307,7 +376,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     const unsigned int pre_base = n_issued;
     if (threadIdx.x == 0) fence_proxy_async();
     for (int j = 0; j < npre; ++j) {
-      issue_ab_part(j, n_issued % S, cur ^ 1, true, false);
+      issue_ab_part(j, n_issued % S, cur ^ 1, true, false, k);
       ++n_issued;
     }
     PB_STAMP(t_c);
@@ -317,7 +386,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       double v[2] = {acc_d, acc_zr};
       ++seq;
       arrive_target += ncta;
-      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, has_nbr);
+      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
       PB_STAMP(t_r2);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -328,7 +397,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     }
     // part 2 of the prefetch: everybody's r (ours, our neighbours' ring values) is final and acquired
     if (threadIdx.x == 0) fence_proxy_async();
-    for (int j = 0; j < npre; ++j) issue_ab_part(j, (pre_base + j) % S, cur ^ 1, false, true);
+    for (int j = 0; j < npre; ++j) issue_ab_part(j, (pre_base + j) % S, cur ^ 1, false, true, k);
     cur ^= 1;
     if (stop) break;
     if (diff_norm < delta) {
@@ -342,6 +411,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   drain();
 
   if (cta == 0 && threadIdx.x == 0 && tma_ok) {
+    if (ctl->red[2] != 0.0) status = PB_STATUS_WATCHDOG;
     ctl->iter = (int)k;
     ctl->status = status;
     ctl->diff_norm = diff_norm;

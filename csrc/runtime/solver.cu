@@ -115,10 +115,12 @@ void Solver::finalize() {
         const LocalBlock nb = make_local_block(grid_.M, grid_.N, pg_, b.nbr[d]);
         c.nbr_r[d] = reinterpret_cast<double*>(static_cast<char*>(peer_base_[b.nbr[d]]) + kHeaderBytes);
         c.nbr_pitch[d] = nb.pitch, c.nbr_nx[d] = nb.nx, c.nbr_ny[d] = nb.ny;
+        c.nbr_halo_cnt[d] = reinterpret_cast<unsigned long long*>(static_cast<char*>(peer_base_[b.nbr[d]]) + kHaloCntOffset) + (d ^ 1);
       }
     }
     c.partials = reinterpret_cast<double*>(arenas_[l] + kPartialsOffset);
     c.arrive = reinterpret_cast<unsigned int*>(arenas_[l] + kArriveOffset);
+    c.halo_cnt = reinterpret_cast<unsigned long long*>(arenas_[l] + kHaloCntOffset);
     c.slots = reinterpret_cast<unsigned long long*>(arenas_[l] + kSlotsOffset);
     for (int rk = 0; rk < nranks(); ++rk)
       if (peer_base_[rk])

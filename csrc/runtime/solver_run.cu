@@ -24,7 +24,10 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   ctas = std::min(ctas, max_tiles);
   if (ctas < 1) throw std::runtime_error("too many virtual ranks for one cooperative launch");
   last_ctas_per_rank_ = ctas;
-  for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
+  for (int l = 0; l < nlocal(); ++l) {
+    PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
+    PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));
+  }
   if (tma)
     PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact, stream));
   else
