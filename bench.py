@@ -248,7 +248,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--M", type=int, default=M_DEFAULT)
     ap.add_argument("--N", type=int, default=N_DEFAULT)
-    ap.add_argument("--grid", default=None, help="PxxPy override of the process grid")
+    ap.add_argument("--grid", default=None, help="process grid: PxxPy, 'reference' (the reference's near-square\n                    choice) or default 'auto' (N x 1 slabs, see parallel/decomp.py)")
     ap.add_argument("--div", default="markstein", choices=["markstein", "true", "recip"],
                     help="stencil divisions by h1/h2: markstein = correctly rounded 3-instruction sequence (same "
                          "bits as 'true'), true = IEEE division, recip = multiply by the reciprocal")

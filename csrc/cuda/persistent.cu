@@ -183,6 +183,12 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
   const int npush = min(ncta, 16);  // mode 2: CTAs that act as "perimeter" CTAs
   unsigned long long base[4];
   for (int d = 0; d < 4; ++d) base[d] = ld_relaxed_sys_u64(c.halo_cnt + d);
+  {  // nobody bumps a counter before everybody has read its base
+    double v[2] = {0.0, 0.0};
+    ++seq;
+    arrive_target += ncta;
+    ok = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, false, false).ok;
+  }
   const unsigned long long t0 = globaltimer_ns();
   for (int it = 0; it < iters && ok; ++it) {
     if (mode == 2 && cta < npush) {

@@ -70,14 +70,13 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + TX - 1) / TX;
   const int ntiles = tiles_x * tiles_y;
   const int nmine = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
-  // Tiles are enumerated perimeter first: a CTA stores its halo values (phase C) and needs its neighbours'
-  // (phase AB) at the start of a phase, so the system-scope release of the stores and the NVLink latency are
-  // hidden behind the interior tiles instead of sitting in front of a reduction.
-  const bool thin = tiles_x <= 2 || tiles_y <= 2;
-  const int n_perim = thin ? ntiles : 2 * tiles_y + 2 * (tiles_x - 2);
-  const int n_my_perim = cta < n_perim ? (n_perim - cta + ncta - 1) / ncta : 0;  // my tiles j < n_my_perim
-  const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
+  // Tile order: row-major, except that the last tile row is visited right after the first one.  The tiles
+  // that store halo rows into the x-neighbours (phase C) and the tiles that need the neighbours' rows
+  // (phase AB) then come first on both sides, so the system-scope release of the stores and the NVLink
+  // latency hide behind the remaining tiles instead of sitting in front of a reduction.  (Enumerating the
+  // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
+  const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
   const bool timing = (cta == 0 && threadIdx.x == 0);
   const int S_pitch = c.pitch;
 
@@ -92,24 +91,24 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 
   auto tile_origin = [&](int j, int& li0, int& lj0) {
     const int t = cta + j * ncta;
-    int tx, ty;
-    if (thin) {
-      tx = t / tiles_y, ty = t - tx * tiles_y;
-    } else if (t < tiles_y) {
-      tx = 0, ty = t;
-    } else if (t < 2 * tiles_y) {
-      tx = tiles_x - 1, ty = t - tiles_y;
-    } else if (t < 2 * tiles_y + (tiles_x - 2)) {
-      tx = 1 + t - 2 * tiles_y, ty = 0;
-    } else if (t < n_perim) {
-      tx = 1 + t - 2 * tiles_y - (tiles_x - 2), ty = tiles_y - 1;
-    } else {
-      const int q = t - n_perim;
-      tx = 1 + q / (tiles_y - 2), ty = 1 + q % (tiles_y - 2);
-    }
+    int tx = t / tiles_y;
+    const int ty = t - tx * tiles_y;
+    if (has_nbr && tiles_x > 2) tx = tx == 0 ? 0 : (tx == 1 ? tiles_x - 1 : tx - 1);
     li0 = 1 + tx * TX;
     lj0 = 1 + ty * TY;
   };
+  // index of my last tile that touches an edge shared with a neighbour (-1: none)
+  int last_halo_j = -1;
+  if (has_nbr) {
+    for (int j = 0; j < nmine; ++j) {
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+      if ((li0 == 1 && c.nbr_r[kXm]) || (li0 + cx - 1 == c.nx && c.nbr_r[kXp]) || (lj0 == 1 && c.nbr_r[kYm]) ||
+          (lj0 + cy - 1 == c.ny && c.nbr_r[kYp]))
+        last_halo_j = j;
+    }
+  }
   // Halo completion counters (see ctx.h): value at launch, and by how much one phase C of the neighbour
   // raises ours (= the number of its tiles along the shared edge).
   unsigned long long halo_base[4];
@@ -355,13 +354,13 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
         }
       }
-      if (has_nbr && j < n_my_perim) {
+      if (has_nbr && j <= last_halo_j) {
         pushed[kXm] += (li0 == 1), pushed[kXp] += (li0 + cx - 1 == c.nx);
         pushed[kYm] += (lj0 == 1), pushed[kYp] += (lj0 + cy - 1 == c.ny);
       }
       __syncthreads();  // stage free; all halo stores of this tile are issued
-      if (has_nbr && j == n_my_perim - 1 && threadIdx.x == 32) {
-        // release the halo stores of all perimeter tiles of this CTA system-wide, then count them in
+      if (has_nbr && j == last_halo_j && threadIdx.x == 32) {
+        // release the halo stores of all edge tiles of this CTA system-wide, then count them in
         fence_acq_rel_sys();
 #pragma unroll
         for (int d = 0; d < 4; ++d)

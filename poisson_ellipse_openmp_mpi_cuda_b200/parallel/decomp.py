@@ -39,10 +39,24 @@ def choose_process_grid(nranks: int) -> tuple[int, int]:
     return px.value, py.value
 
 
-def parse_grid(spec, nranks: int) -> tuple[int, int]:
-    """``None`` -> reference choice; ``"2x4"`` or ``(2, 4)`` -> override (must multiply to ``nranks``)."""
-    if spec is None:
+def nvswitch_process_grid(nranks: int, M: int) -> tuple[int, int]:
+    """Process grid for GPUs behind an NVSwitch (every peer equally close, halo bytes negligible next to HBM
+    traffic): split along x only (``nranks x 1``).  Every shared edge is then a contiguous row of the arrays
+    (coalesced peer stores, no strided column edges) and the edge tiles are the first tiles of every phase, so
+    the release of the halo stores overlaps with the interior.  Falls back to the reference's near-square grid
+    when the slabs would get thinner than one 32-row tile."""
+    if nranks > 1 and (M - 1) // nranks >= 32:
+        return nranks, 1
+    return choose_process_grid(nranks)
+
+
+def parse_grid(spec, nranks: int, M: int | None = None) -> tuple[int, int]:
+    """``None`` / ``"reference"`` -> the reference's choice; ``"auto"`` -> :func:`nvswitch_process_grid`;
+    ``"2x4"`` or ``(2, 4)`` -> explicit (must multiply to ``nranks``)."""
+    if spec is None or spec == "reference":
         return choose_process_grid(nranks)
+    if spec == "auto":
+        return nvswitch_process_grid(nranks, M if M is not None else 1 << 30)
     if isinstance(spec, str):
         a, b = spec.lower().split("x")
         spec = (int(a), int(b))

@@ -47,9 +47,9 @@ def world_info() -> tuple[int, int]:
 class FusedMultiGpuSolver:
     """One rank of the fused multi-GPU solver (peer-memory halo + in-kernel reductions)."""
 
-    def __init__(self, M: int, N: int, grid=None, device: int | None = None):
+    def __init__(self, M: int, N: int, grid="auto", device: int | None = None):
         self.rank, self.world = world_info()
-        self.Px, self.Py = parse_grid(grid, self.world)
+        self.Px, self.Py = parse_grid("auto" if grid is None else grid, self.world, M)
         self.M, self.N = M, N
         self.device = torch.cuda.current_device() if device is None else device
         self.solver = GpuSolver(M, N, self.Px, self.Py, first_rank=self.rank, nlocal=1, device=self.device)
