@@ -50,6 +50,10 @@ cudaError_t launch_pack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, double
 cudaError_t launch_unpack_edges(const RankCtx* d_ctx, const RankCtx& h_ctx, const double* recvbuf, int stride,
                                 cudaStream_t stream);
 
+// stand-alone Ap = A p with fused (Ap, p) (apply_a_op.cu); scratch: apply_a_tiles(nx, ny) doubles
+int apply_a_tiles(int nx, int ny);
+cudaError_t launch_apply_a_dot(int M, int N, int nx, int ny, int pitch, const double* p, const double* a,
+                               const double* b, double* Ap, double* dot_out, double* scratch, cudaStream_t stream);
 // unit test of the division sequences (step_kernels.cu)
 cudaError_t launch_div_check(double h, unsigned long long n, unsigned long long seed, unsigned long long* counts,
                              cudaStream_t stream);

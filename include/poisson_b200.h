@@ -158,6 +158,13 @@ int pb_step_scalars(pb_solver* s, int local_idx, int phase /* 0 init, 1 alpha, 2
 int pb_step_pack_edges(pb_solver* s, int local_idx, void* dev_buf, int stride, void* cuda_stream);
 int pb_step_unpack_edges(pb_solver* s, int local_idx, const void* dev_buf, int stride, void* cuda_stream);
 int pb_step_error_report(pb_solver* s, int local_idx, void* cuda_stream);
+/* ---- stand-alone operator: Ap = A p and dot = h1 h2 sum(Ap * p) on one block in the padded layout
+ *      (replaces apply_A_kernel S4:507-536 + dot_gpu(Ap, p) S4:771-786).  All pointers are device pointers;
+ *      p, a, b, Ap are (nx+2) x pitch doubles, dot_out is one double.  Stream-ordered; the per-tile scratch
+ *      (one double per 32 x 64 tile) is taken from the stream's memory pool for the duration of the call. ---- */
+int pb_apply_A_dot(int M, int N, int nx, int ny, int pitch, const void* p, const void* a, const void* b, void* Ap,
+                   void* dot_out, void* cuda_stream);
+
 /* communication micro-benchmark (collective over all ranks): `iters` rounds of the in-kernel cross-rank
  * reduction (mode 0) or of halo stores of `edge` doubles per neighbour + reduction (mode 1);
  * out2 = {ns per round measured on this rank, checksum}.  ctas = 0: one CTA per SM. */

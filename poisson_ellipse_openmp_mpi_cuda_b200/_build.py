@@ -35,6 +35,7 @@ LIB_SOURCES = [
     "cuda/step_kernels.cu",
     "cuda/persistent.cu",
     "cuda/persistent_tma.cu",
+    "cuda/apply_a_op.cu",
     "runtime/fabric.cu",
     "runtime/solver.cu",
     "runtime/solver_run.cu",

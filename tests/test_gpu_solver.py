@@ -153,3 +153,38 @@ def test_large_grid_800x1200():
     assert res["iters"] == 989
     _check_errors(res, (800, 1200))
     s.close()
+
+
+def test_apply_A_dot_operator_matches_fp32_free_reference(native):
+    """Stand-alone Ap = A p + (Ap, p): against a plain PyTorch evaluation of the same stencil (fp64) and the CPU
+    routine of the oracle."""
+    from poisson_ellipse_openmp_mpi_cuda_b200.ops.operators import apply_A_dot
+
+    M, N = 200, 300
+    s = _solver(M, N).finalize()
+    s.step("assemble")
+    torch.cuda.synchronize()
+    a, b = s.array("a").clone(), s.array("b").clone()
+    blk, co = s.block(), s.col_off
+    g = torch.Generator(device="cuda").manual_seed(7)
+    p = torch.zeros_like(a)
+    p[1:blk.nx + 1, co + 1:co + 1 + blk.ny] = torch.rand((blk.nx, blk.ny), dtype=torch.float64, device="cuda", generator=g)
+    Ap, dot = apply_A_dot(M, N, p, a, b)
+    h1, h2 = 2.0 / M, 1.2 / N
+    I, J = slice(1, blk.nx + 1), slice(co + 1, co + 1 + blk.ny)
+    Ip, Im = slice(2, blk.nx + 2), slice(0, blk.nx)
+    Jp, Jm = slice(co + 2, co + 2 + blk.ny), slice(co, co + blk.ny)
+    ax = -1.0 / h1 * (a[Ip, J] * (p[Ip, J] - p[I, J]) / h1 - a[I, J] * (p[I, J] - p[Im, J]) / h1)
+    ay = -1.0 / h2 * (b[I, Jp] * (p[I, Jp] - p[I, J]) / h2 - b[I, J] * (p[I, J] - p[I, Jm]) / h2)
+    ref = ax + ay
+    assert torch.allclose(Ap[I, J], ref, rtol=1e-13, atol=1e-9)
+    assert dot.item() == pytest.approx((ref * p[I, J]).sum().item() * h1 * h2, rel=1e-12)
+    # CPU oracle routine on the same data
+    nb = native.Block()
+    native.lib().pb_local_block(M, N, 1, 1, 0, C.byref(nb))
+    ph, ah, bh = p.cpu(), a.cpu(), b.cpu()
+    Aph = torch.zeros_like(ph)
+    s_cpu = native.lib().pb_cpu_apply_A_local(M, N, C.byref(nb), ph.data_ptr(), ah.data_ptr(), bh.data_ptr(), Aph.data_ptr(), 1)
+    assert torch.allclose(Ap.cpu()[I, J], Aph[I, J], rtol=1e-13, atol=1e-9)
+    assert dot.item() == pytest.approx(s_cpu * h1 * h2, rel=1e-12)
+    s.close()
