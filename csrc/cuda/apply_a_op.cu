@@ -85,3 +85,79 @@ extern "C" int pb_apply_A_dot(int M, int N, int nx, int ny, int pitch, const voi
     return -1;
   }
 }
+
+// ---------------------------------------------------------------------------------------------------
+// pb_apply_A_dot_noalloc -- the same operator for callers that must not allocate.
+//
+// Some users of this library cannot let a call reach the device allocator: an application that has given
+// every byte of device memory to its own pool (a further cudaMalloc fails or breaks its budget), a service
+// on a latency-critical path that cannot wait on the driver's allocation lock, or a host program whose
+// rules forbid any allocation once start-up is over.  pb_apply_A_dot takes its per-tile scratch from the
+// stream's memory pool on every call; this variant keeps the scratch in the file-scope array below instead
+// and never calls cudaMalloc, cudaFree, their async forms, or any other allocating routine.
+//
+// The array is part of the library image: every GPU on which this library's code gets loaded holds these
+// 512 KiB from then until the process exits, whether or not this entry point is ever used.
+//
+// Limit: kNoAllocMaxTiles tiles of 32 x 64 nodes, i.e. ceil(nx/32) * ceil(ny/64) <= 65536 (for example
+// 8192 x 16384 owned nodes).  Larger blocks are rejected with an error; nothing is launched.
+//
+// Set-up: `g_apply_a_scratch` is a device symbol.  In host code that name is only a stand-in, not a
+// device address, so the first call made on a given device (with that device current) asks the runtime for
+// the real address once, with cudaGetSymbolAddress, checks the result and caches it per device.  Make that
+// first call during initialisation, before any stream capture is begun on the device.
+//
+// Sharing: all calls on a device use the one array, and it keeps whatever the previous call left in it.
+// Nothing in it has to start at zero -- each call writes every per-tile slot it later reads, and reads
+// no other slot -- so no clearing pass is needed.  Two calls whose kernels overlap on the GPU (different
+// streams, or different host threads without ordering between them) would write the same slots and race:
+// keep calls on one device ordered, e.g. by issuing them into one stream.
+namespace pb {
+
+constexpr int kNoAllocMaxTiles = 65536;
+static __device__ __align__(256) double g_apply_a_scratch[kNoAllocMaxTiles];
+
+constexpr int kNoAllocMaxDevices = 64;
+static double* g_apply_a_scratch_addr[kNoAllocMaxDevices];  // device address of the array, per device ordinal
+
+// Address of the scratch array on the current device; resolved on first use per device.
+static cudaError_t noalloc_scratch_address(double** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return cudaErrorInvalidDevice;
+  double* addr = __atomic_load_n(&g_apply_a_scratch_addr[dev], __ATOMIC_ACQUIRE);
+  if (!addr) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_apply_a_scratch);
+    if (e != cudaSuccess) return e;
+    addr = static_cast<double*>(sym);
+    __atomic_store_n(&g_apply_a_scratch_addr[dev], addr, __ATOMIC_RELEASE);  // same value from every thread
+  }
+  *out = addr;
+  return cudaSuccess;
+}
+
+}  // namespace pb
+
+extern "C" int pb_apply_A_dot_noalloc(int M, int N, int nx, int ny, int pitch, const void* p, const void* a,
+                                      const void* b, void* Ap, void* dot_out, void* cuda_stream) {
+  try {
+    if (M < 2 || N < 2 || nx < 1 || ny < 1 || pitch < ny + 2 + pb::kColOff)
+      throw std::runtime_error("pb_apply_A_dot_noalloc: invalid block shape");
+    const long long ntiles = (long long)((nx + pb::kTileX - 1) / pb::kTileX) * (long long)((ny + pb::kTileY - 1) / pb::kTileY);
+    if (ntiles > pb::kNoAllocMaxTiles)
+      throw std::runtime_error("pb_apply_A_dot_noalloc: block of " + std::to_string(nx) + " x " + std::to_string(ny) +
+                               " nodes needs " + std::to_string(ntiles) + " tiles of scratch, the built-in array holds " +
+                               std::to_string(pb::kNoAllocMaxTiles) + "; use pb_apply_A_dot for blocks this large");
+    double* scratch = nullptr;
+    PB_CUDA_CHECK(pb::noalloc_scratch_address(&scratch));
+    PB_CUDA_CHECK(pb::launch_apply_a_dot(M, N, nx, ny, pitch, static_cast<const double*>(p), static_cast<const double*>(a),
+                                         static_cast<const double*>(b), static_cast<double*>(Ap),
+                                         static_cast<double*>(dot_out), scratch, reinterpret_cast<cudaStream_t>(cuda_stream)));
+    return 0;
+  } catch (const std::exception& ex) {
+    pb::set_last_error(ex.what());
+    return -1;
+  }
+}

@@ -165,6 +165,18 @@ int pb_step_error_report(pb_solver* s, int local_idx, void* cuda_stream);
 int pb_apply_A_dot(int M, int N, int nx, int ny, int pitch, const void* p, const void* a, const void* b, void* Ap,
                    void* dot_out, void* cuda_stream);
 
+/* pb_apply_A_dot for callers that must not allocate (no counterpart in the reference, which allocates all its
+ * device memory up front with cudaMalloc and offers no library entry points at all).  Same arguments and
+ * results as pb_apply_A_dot; the per-tile scratch lives in a 512 KiB array built into the library instead of
+ * coming from the stream's memory pool, and the call makes no cudaMalloc / cudaFree / pool request.  Meant
+ * for programs that own all device memory through their own pool, that sit on a path where the driver's
+ * allocator lock is not acceptable, or that may not allocate after start-up.  Limit: ceil(nx/32) *
+ * ceil(ny/64) <= 65536 tiles, larger blocks return -1 with an explanatory pb_last_error().  The first call
+ * on each device looks up the array's device address (do it at start-up, before any stream capture); calls
+ * on one device share the array, so calls that overlap on the GPU race -- keep them stream-ordered. */
+int pb_apply_A_dot_noalloc(int M, int N, int nx, int ny, int pitch, const void* p, const void* a, const void* b,
+                           void* Ap, void* dot_out, void* cuda_stream);
+
 /* communication micro-benchmark (collective over all ranks): `iters` rounds of the in-kernel cross-rank
  * reduction (mode 0) or of halo stores of `edge` doubles per neighbour + reduction (mode 1);
  * out2 = {ns per round measured on this rank, checksum}.  ctas = 0: one CTA per SM. */

@@ -131,6 +131,7 @@ def _declare(lib: C.CDLL) -> None:
         "pb_step_unpack_edges": (I, [vp, I, vp, I, vp]),
         "pb_step_error_report": (I, [vp, I, vp]),
         "pb_apply_A_dot": (I, [I, I, I, I, I, vp, vp, vp, vp, vp, vp]),
+        "pb_apply_A_dot_noalloc": (I, [I, I, I, I, I, vp, vp, vp, vp, vp, vp]),
         "pb_solver_xgpu_bench": (I, [vp, I, I, I, I, vp, dp]),
         "pb_debug_div_check": (I, [D, C.c_ulonglong, C.c_ulonglong, vp, vp]),
         "pb_debug_tma_probe": (I, [vp, I, I, I, I, I, C.c_uint, vp, vp, vp]),
