@@ -87,6 +87,7 @@ int pb_solver_solve(pb_solver* s, const pb_solve_options* o, void* stream, pb_st
     opt.ctas_per_sm = o->ctas_per_sm;
     opt.error_report = o->error_report;
     opt.tile_rows = o->tile_rows;
+    opt.l2_hints = o->l2_hints;
     opt.watchdog_s = o->watchdog_s;
     s->impl.solve(opt, as_stream(stream), stats);
   });
@@ -147,6 +148,7 @@ int pb_group_solve(pb_group* g, const pb_solve_options* o, pb_stats* stats) {
     opt.ctas_per_sm = o->ctas_per_sm;
     opt.error_report = o->error_report;
     opt.tile_rows = o->tile_rows;
+    opt.l2_hints = o->l2_hints;
     opt.watchdog_s = o->watchdog_s;
     g->impl.solve(opt, stats);
   });

@@ -42,7 +42,7 @@ struct TmaCfg {
 
 template <int TX, int DIV>
 __global__ void __launch_bounds__(kThreads, 1)
-pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant) {
+pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints) {
   using Cfg = TmaCfg<TX>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
@@ -63,7 +63,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     mbar_fence_init();
   }
   __syncthreads();
-  unsigned char* stage_base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(s_dyn) + 127) & ~uintptr_t(127));
+  // s_dyn is declared __align__(128); deriving every stage pointer from it by plain pointer arithmetic keeps
+  // the accesses in the shared address space (LDS/STS instead of generic LD/ST)
+  unsigned char* const stage_base = s_dyn;
   const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * 12;
 
   Control* ctl = c.ctl;
@@ -86,6 +88,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const int norm = ctl->norm;
   const double h1h2 = c.g.h1h2;
   const StencilConsts K = make_stencil_consts(c.g);
+
+  // L2 policy per operand: what both phases of every iteration re-read (r, D, p) is kept, what is touched once
+  // per iteration (a, b, w, Ap after its single use) is marked evict-first, so that on a working set around
+  // the L2 size (4096^2 over 8 GPUs: 134 MB per GPU vs 126 MB) the re-read part stays resident.
+  const uint64_t pol_keep = l2_hints ? kL2EvictLast : kL2EvictNormal;
+  const uint64_t pol_stream = l2_hints ? kL2EvictFirst : kL2EvictNormal;
 
   unsigned int n_issued = 0, n_consumed = 0;  // uniform across the CTA
 
@@ -152,17 +160,17 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (part1) {
         fence_proxy_async_smem();
         mbar_arrive_expect_tx(bar, Cfg::kTxAB);
-        tma_load_2d(sb + Cfg::kExtBytes, maps + kMapDExt, x, y, bar);
-        tma_load_2d(sb + 2 * Cfg::kExtBytes, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar);
-        tma_load_2d(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 2, y + 1, bar);
-        tma_load_2d(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 2, y + 1, bar);
+        tma_load_2d_hint(sb + Cfg::kExtBytes, maps + kMapDExt, x, y, bar, pol_keep);
+        tma_load_2d_hint(sb + 2 * Cfg::kExtBytes, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar, pol_keep);
+        tma_load_2d_hint(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 2, y + 1, bar, pol_stream);
+        tma_load_2d_hint(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 2, y + 1, bar, pol_stream);
       }
       if (part2) {
         if (has_nbr) {
           wait_halo(li0, lj0, rounds);
           fence_proxy_async();  // the neighbours' generic-proxy stores, just acquired -> TMA read
         }
-        tma_load_2d(sb, maps + kMapRExt, x, y, bar);
+        tma_load_2d_hint(sb, maps + kMapRExt, x, y, bar, pol_keep);
       }
     }
   };
@@ -180,11 +188,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       fence_proxy_async_smem();
       mbar_arrive_expect_tx(bar, Cfg::kTxC);
       const int x = kColOff + lj0, y = li0;
-      tma_load_2d(sb, maps + kMapW, x, y, bar);
-      tma_load_2d(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar);
-      tma_load_2d(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar);
-      tma_load_2d(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar);
-      tma_load_2d(sb + 4 * Cfg::kTileBytes, maps + kMapD, x, y, bar);
+      tma_load_2d_hint(sb, maps + kMapW, x, y, bar, pol_stream);
+      tma_load_2d_hint(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar, pol_keep);
+      tma_load_2d_hint(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar, pol_keep);
+      tma_load_2d_hint(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar, pol_stream);
+      tma_load_2d_hint(sb + 4 * Cfg::kTileBytes, maps + kMapD, x, y, bar, pol_keep);
     }
     ++n_issued;
   };
@@ -263,30 +271,55 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       int li0, lj0;
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
-      // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory
-      for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) {
+      // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory.
+      //    Full tiles take fixed-trip loops that the compiler unrolls, so the dependent fp64 chains of several
+      //    cells are in flight per thread (16 warps per SM do not hide them otherwise).
+      const bool full = (cx == TX) && (cy == TY);
+      auto ab_cell = [&](int e) {
         const int row = e / EC, col = e - row * EC - 1;  // col 0 = left ring column of the tile
-        if (col < 0 || col >= cy + 2) continue;
+        if (col < 0 || col >= cy + 2) return;
         const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
-        if (!(row_in || col_in)) continue;
-        const double v = fma(beta, s_p[e], safe_div(s_r[e], s_D[e]));
+        if (!(row_in || col_in)) return;
+        const double v = fma(beta, s_p[e], div_var<DIV>(s_r[e], s_D[e]));
         s_p[e] = v;
         const int li = li0 - 1 + row, lj = lj0 - 1 + col;
         const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
         if ((row_in && col_in) || ring) pout[(size_t)li * S_pitch + (lj + kColOff)] = v;
+      };
+      if (full) {
+        constexpr int kCells = (TX + 2) * EC;
+#pragma unroll
+        for (int k = 0; k < (kCells + kThreads - 1) / kThreads; ++k) {
+          const int e = threadIdx.x + k * kThreads;
+          if (e < kCells) ab_cell(e);
+        }
+      } else {
+        for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) ab_cell(e);
       }
       __syncthreads();
       // 2. Ap = A p_new on the owned nodes of the tile
       {
         const int col = threadIdx.x % TY + 1;
-        if (col <= cy) {
+        auto ab_node = [&](int row, double& pc) {
+          const double* s = s_p + row * EC + col + 1;
+          pc = s[0];
+          const double v = stencil_value<DIV>(K, pc, s[-EC], s[EC], s[-1], s[1], s_a[(row - 1) * TY + (col - 1)],
+                                              s_a[row * TY + (col - 1)], s_b[(row - 1) * BC + (col - 1)],
+                                              s_b[(row - 1) * BC + col]);
+          c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
+          return v;
+        };
+        if (full) {
+          constexpr int kPer = TX / (kThreads / TY);  // nodes per thread
+          double v[kPer], pc[kPer];
+#pragma unroll
+          for (int k = 0; k < kPer; ++k) v[k] = ab_node(threadIdx.x / TY + 1 + k * (kThreads / TY), pc[k]);
+#pragma unroll
+          for (int k = 0; k < kPer; ++k) acc_ab = fma(v[k], pc[k], acc_ab);  // same order as the generic loop
+        } else if (col <= cy) {
           for (int row = threadIdx.x / TY + 1; row <= cx; row += kThreads / TY) {
-            const double* s = s_p + row * EC + col + 1;
-            const double pc = s[0], pim = s[-EC], pip = s[EC], pjm = s[-1], pjp = s[1];
-            const double a_c = s_a[(row - 1) * TY + (col - 1)], a_ip = s_a[row * TY + (col - 1)];
-            const double b_c = s_b[(row - 1) * BC + (col - 1)], b_jp = s_b[(row - 1) * BC + col];
-            const double v = stencil_value<DIV>(K, pc, pim, pip, pjm, pjp, a_c, a_ip, b_c, b_jp);
-            c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
+            double pc;
+            const double v = ab_node(row, pc);
             acc_ab = fma(v, pc, acc_ab);
           }
         }
@@ -333,25 +366,46 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
       const int col = threadIdx.x % TY;
-      if (col < cy) {
-        for (int row = threadIdx.x / TY; row < cx; row += kThreads / TY) {
-          const int e = row * TY + col;
-          const int li = li0 + row, lj = lj0 + col;
-          const size_t g = (size_t)li * S_pitch + (lj + kColOff);
-          const double w_old = s_w[e];
-          const double w_new = fma(alpha, s_p[e], w_old);
-          const double r_new = fma(-alpha, s_Ap[e], s_r[e]);
+      const bool full = (cx == TX) && (cy == TY);
+      // loads and arithmetic of one node; stores and halo stores included
+      auto c_node = [&](int row, double& d_out, double& z_out, double& r_out) {
+        const int e = row * TY + col;
+        const int li = li0 + row, lj = lj0 + col;
+        const size_t g = (size_t)li * S_pitch + (lj + kColOff);
+        const double w_old = s_w[e];
+        const double w_new = fma(alpha, s_p[e], w_old);
+        const double r_new = fma(-alpha, s_Ap[e], s_r[e]);
+        if (l2_hints)
+          __stcs(&c.w[g], w_new);  // streaming store: w is not read again before the next iteration's phase C
+        else
           c.w[g] = w_new;
-          c.r[g] = r_new;
-          const double d = __dsub_rn(w_new, w_old);
+        c.r[g] = r_new;
+        d_out = __dsub_rn(w_new, w_old);
+        z_out = div_var<DIV>(r_new, s_D[e]);
+        r_out = r_new;
+        if (li == 1 && c.nbr_r[kXm])
+          c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
+        if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
+        if (lj == 1 && c.nbr_r[kYm])
+          c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
+        if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+      };
+      if (full) {
+        constexpr int kPer = TX / (kThreads / TY);
+        double d[kPer], z[kPer], rn[kPer];
+#pragma unroll
+        for (int k = 0; k < kPer; ++k) c_node(threadIdx.x / TY + k * (kThreads / TY), d[k], z[k], rn[k]);
+#pragma unroll
+        for (int k = 0; k < kPer; ++k) {
+          acc_d = fma(d[k], d[k], acc_d);
+          acc_zr = fma(z[k], rn[k], acc_zr);
+        }
+      } else if (col < cy) {
+        for (int row = threadIdx.x / TY; row < cx; row += kThreads / TY) {
+          double d, z, rn;
+          c_node(row, d, z, rn);
           acc_d = fma(d, d, acc_d);
-          acc_zr = fma(safe_div(r_new, s_D[e]), r_new, acc_zr);
-          if (li == 1 && c.nbr_r[kXm])
-            c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
-          if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
-          if (lj == 1 && c.nbr_r[kYm])
-            c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
-          if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+          acc_zr = fma(z, rn, acc_zr);
         }
       }
       if (has_nbr && j <= last_halo_j) {
@@ -432,25 +486,26 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 
 // ---------------------------------------------------------------------------------------------------
 template <int TX, int DIV>
-static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, cudaStream_t stream) {
+static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int l2_hints,
+                                  cudaStream_t stream) {
   const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV>;
   const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant};
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints};
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
 }
 
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
-                                  cudaStream_t stream) {
+                                  int l2_hints, cudaStream_t stream) {
   if (tile_rows == 32) {
-    if (div == kDivTrue) return launch_variant<32, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
-    if (div == kDivMarkstein) return launch_variant<32, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
-    return launch_variant<32, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 0, stream);
+    if (div == kDivTrue) return launch_variant<32, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 0, l2_hints, stream);
+    if (div == kDivMarkstein) return launch_variant<32, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 0, l2_hints, stream);
+    return launch_variant<32, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 0, l2_hints, stream);
   }
-  if (div == kDivTrue) return launch_variant<16, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
-  if (div == kDivMarkstein) return launch_variant<16, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
-  return launch_variant<16, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 1, stream);
+  if (div == kDivTrue) return launch_variant<16, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 1, l2_hints, stream);
+  if (div == kDivMarkstein) return launch_variant<16, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 1, l2_hints, stream);
+  return launch_variant<16, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 1, l2_hints, stream);
 }
 
 // Debug / unit-test probe: one box load through a tensor map at (x, y) into shared memory, copied out to

@@ -66,6 +66,20 @@ __device__ __forceinline__ double div_const(double x, double h, double y) {
   return fma(fma(-q, h, x), y, q);
 }
 
+// z = r / D with a per-node divisor.  kDivTrue: IEEE division (on this data its out-of-line slow path runs
+// often: residuals are zero or tiny next to D ~ 1e7, and the profile showed 13 % of all issued instructions
+// there).  Otherwise: y = RN(1/D) from __drcp_rn -- its range check looks at D only, which is always an
+// ordinary number -- followed by the same Markstein correction as div_const.  Same bits as the division
+// unless |r/D| is near the subnormal range (never the case before convergence: r >= 1e-20, D <= 1e9).
+template <int DIV>
+__device__ __forceinline__ double div_var(double r, double D) {
+  if (DIV == kDivTrue) return D != 0.0 ? r / D : 0.0;
+  const double y = __drcp_rn(D);
+  const double q = __dmul_rn(r, y);
+  const double z = fma(fma(-q, D, r), y, q);
+  return D != 0.0 ? z : 0.0;
+}
+
 // (A p) at one node, association of the reference (S4:526-535).
 template <int DIV>
 __device__ __forceinline__ double stencil_value(const StencilConsts& k, double pc, double pim, double pip, double pjm,
@@ -99,7 +113,7 @@ __device__ __forceinline__ double phase_ab_tile(const RankCtx& c, int tile, doub
     const size_t g = (size_t)li * S + (lj + kColOff);
     double v;
     if (FUSE_P) {
-      v = fma(beta, __ldcg(&pin[g]), safe_div(__ldcg(&c.r[g]), __ldg(&c.D[g])));
+      v = fma(beta, __ldcg(&pin[g]), div_var<DIV>(__ldcg(&c.r[g]), __ldg(&c.D[g])));
       const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
       if ((row_in && col_in) || ring) pout[g] = v;
     } else {

@@ -29,7 +29,8 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
     PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));
   }
   if (tma)
-    PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact, stream));
+    PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact,
+                                        opt.l2_hints, stream));
   else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;

@@ -116,6 +116,8 @@ typedef struct pb_solve_options {
   int error_report;   /* 1: compute the error against the analytic solution after the solve */
   int tile_rows;      /* TMA persistent kernel: 32 (2 pipeline stages) or 16 (4 stages); 0 = auto */
   double watchdog_s;  /* 0 = default (20 s): device-side waits give up after this long */
+  int l2_hints;       /* 1: TMA loads carry L2 eviction priorities (keep r, D, p; stream a, b, w, Ap) */
+  int reserved;
 } pb_solve_options;
 
 int pb_cuda_device_count(void);

@@ -72,6 +72,8 @@ class SolveOptions(C.Structure):
         ("error_report", C.c_int),
         ("tile_rows", C.c_int),
         ("watchdog_s", C.c_double),
+        ("l2_hints", C.c_int),
+        ("reserved", C.c_int),
     ]
 
 
