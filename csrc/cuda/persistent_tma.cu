@@ -127,12 +127,14 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     edge_tiles[d] = c.nbr_r[d] ? (d < 2 ? (c.nbr_ny[d] + TY - 1) / TY : (c.nbr_nx[d] + TX - 1) / TX) : 0;
   }
   // thread 0: wait until the ring cells of the tile at (li0, lj0) hold the neighbours' r of round `rounds`
-  auto wait_halo = [&](int li0, int lj0, long long rounds) {
+  auto wait_halo = [&](int li0, int lj0, long long rounds) -> bool {
     const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
     const bool touch[4] = {li0 == 1, li0 + cx - 1 == c.nx, lj0 == 1, lj0 + cy - 1 == c.ny};
+    bool waited = false;
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
       if (!touch[d] || !c.nbr_r[d]) continue;
+      waited = true;
       const unsigned long long want = halo_base[d] + (unsigned long long)rounds * (unsigned long long)edge_tiles[d];
       unsigned long long t0 = 0;
       unsigned int spins = 0;
@@ -147,6 +149,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         }
       }
     }
+    return waited;
   };
   // Phase-AB loads of tile j into stage `st`.  part 1 = everything that does not depend on the other CTAs'
   // phase C (D, p, a, b; arms the barrier with the full byte count), part 2 = the r box.
@@ -166,10 +169,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         tma_load_2d_hint(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 2, y + 1, bar, pol_stream);
       }
       if (part2) {
-        if (has_nbr) {
-          wait_halo(li0, lj0, rounds);
-          fence_proxy_async();  // the neighbours' generic-proxy stores, just acquired -> TMA read
-        }
+        // only a tile on a shared edge reads cells another GPU wrote since the phase-start fence
+        if (has_nbr && wait_halo(li0, lj0, rounds)) fence_proxy_async();  // acquired generic-proxy stores -> TMA read
         tma_load_2d_hint(sb, maps + kMapRExt, x, y, bar, pol_keep);
       }
     }
@@ -413,8 +414,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         pushed[kYm] += (lj0 == 1), pushed[kYp] += (lj0 + cy - 1 == c.ny);
       }
       __syncthreads();  // stage free; all halo stores of this tile are issued
-      if (has_nbr && j == last_halo_j && threadIdx.x == 32) {
-        // release the halo stores of all edge tiles of this CTA system-wide, then count them in
+      // Release the halo stores of this CTA's edge tiles system-wide and count them in at the neighbour --
+      // one tile after the last edge tile (or at the end of the phase), when the stores have long been
+      // acknowledged and the fence costs little; the whole CTA would otherwise wait for it at the next barrier.
+      if (has_nbr && last_halo_j >= 0 && (j == last_halo_j + 1 || (j == nmine - 1 && last_halo_j == nmine - 1)) &&
+          threadIdx.x == 32) {
         fence_acq_rel_sys();
 #pragma unroll
         for (int d = 0; d < 4; ++d)

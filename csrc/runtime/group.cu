@@ -81,6 +81,8 @@ void DeviceGroup::solve(const SolveOptions& opt, pb_stats* out) {
     out->t_dot = std::max(out->t_dot, s.t_dot);
     out->t_assemble = std::max(out->t_assemble, s.t_assemble);
     out->t_iterations = std::max(out->t_iterations, s.t_iterations);
+    out->t_phase_ab = std::max(out->t_phase_ab, s.t_phase_ab), out->t_phase_c = std::max(out->t_phase_c, s.t_phase_c);
+    out->t_red1 = std::max(out->t_red1, s.t_red1), out->t_red2 = std::max(out->t_red2, s.t_red2);
   }
   out->l2_in_D = std::sqrt(grid_.h1h2 * out->sum_e2_in_D);
   out->l2_all = std::sqrt(grid_.h1h2 * out->sum_e2_all);

@@ -145,6 +145,8 @@ void Solver::collect(cudaStream_t stream, pb_stats* out) {
     out->t_dot = 1e-9 * (double)(t_r1 + t_r2 + t_init);
     out->t_comm = nranks() > 1 ? 1e-9 * (double)(t_r1 + t_r2) : 0.0;
     out->t_precond = 0.25 * 1e-9 * (double)t_c;  // attributed share of phase C (one of its four streams)
+    out->t_phase_ab = 1e-9 * (double)t_ab, out->t_phase_c = 1e-9 * (double)t_c;
+    out->t_red1 = 1e-9 * (double)t_r1, out->t_red2 = 1e-9 * (double)t_r2;
   } else {
     out->t_gpu = 1e-3 * ms_iter;
   }

@@ -48,6 +48,8 @@ typedef struct pb_stats {
   double t_iterations; /* the PCG loop alone (CUDA events) */
   double sum_e2_in_D; /* raw sums of squared errors over the local ranks, for cross-process reduction */
   double sum_e2_all;
+  /* persistent kernels: device-clock split of the iteration (CTA 0 of the slowest rank) */
+  double t_phase_ab, t_phase_c, t_red1, t_red2;
 } pb_stats;
 
 /* Local block of the 2-D decomposition in the padded layout (see csrc/core/decomp.h). */

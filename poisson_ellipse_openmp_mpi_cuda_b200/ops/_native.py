@@ -37,6 +37,10 @@ class Stats(C.Structure):
         ("t_iterations", C.c_double),
         ("sum_e2_in_D", C.c_double),
         ("sum_e2_all", C.c_double),
+        ("t_phase_ab", C.c_double),
+        ("t_phase_c", C.c_double),
+        ("t_red1", C.c_double),
+        ("t_red2", C.c_double),
     ]
 
     def as_dict(self) -> dict:

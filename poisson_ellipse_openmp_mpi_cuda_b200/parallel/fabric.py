@@ -80,7 +80,7 @@ class FusedMultiGpuSolver:
 
 _SUM_KEYS = ("sum_e2_in_D", "sum_e2_all", "nodes_in_D")
 _MAX_KEYS = ("max_abs", "max_w", "seconds", "t_gpu", "t_copy", "t_comm", "t_precond", "t_dot", "t_assemble",
-             "t_iterations")
+             "t_iterations", "t_phase_ab", "t_phase_c", "t_red1", "t_red2")
 
 
 def combine_reports(res: dict, M: int, N: int, device="cpu") -> dict:
@@ -89,7 +89,7 @@ def combine_reports(res: dict, M: int, N: int, device="cpu") -> dict:
     if world == 1:
         return res
     sums = torch.tensor([float(res[k]) for k in _SUM_KEYS], dtype=torch.float64, device=device)
-    maxs = torch.tensor([float(res[k]) for k in _MAX_KEYS], dtype=torch.float64, device=device)
+    maxs = torch.tensor([float(res.get(k, 0.0)) for k in _MAX_KEYS], dtype=torch.float64, device=device)
     dist.all_reduce(sums, op=dist.ReduceOp.SUM)
     dist.all_reduce(maxs, op=dist.ReduceOp.MAX)
     out = dict(res)
