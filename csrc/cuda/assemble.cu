@@ -15,6 +15,8 @@ __global__ void __launch_bounds__(256) assemble_kernel(const RankCtx* __restrict
   const RankCtx& c = *ctx;
   const int rows = c.nx + 2, cols = c.ny + 2;
   const long long total = (long long)rows * cols;
+  const double inv_eps = 1.0 / c.g.eps;
+  const double d_in = diag_from_faces(c.g, 1.0, 1.0, 1.0, 1.0), d_out = diag_from_faces(c.g, inv_eps, inv_eps, inv_eps, inv_eps);
   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
        e += (long long)gridDim.x * blockDim.x) {
     const int li = (int)(e / cols), lj = (int)(e - (long long)li * cols);
@@ -30,6 +32,10 @@ __global__ void __launch_bounds__(256) assemble_kernel(const RankCtx* __restrict
       rhs = rhs_value(c.g, gi, gj);
     }
     c.D[g] = d;
+    const unsigned int ka = a_c == 1.0 ? 0u : (a_c == inv_eps ? 1u : 2u);
+    const unsigned int kb = b_c == 1.0 ? 0u : (b_c == inv_eps ? 1u : 2u);
+    const unsigned int kd = d == d_in ? 0u : (d == d_out ? 1u : 2u);
+    c.cls[g] = (unsigned char)(ka | (kb << 2) | (kd << 4));
     c.r[g] = rhs;
     c.w[g] = 0.0;
     c.p[0][g] = 0.0;

@@ -61,6 +61,11 @@ struct RankCtx {
   int nbr[4];  // neighbour ranks (x-, x+, y-, y+), -1 at the boundary of Omega
   // local arrays, all (nx+2) x pitch
   double *w, *r, *p[2], *Ap, *a, *b, *D;
+  // Coefficient classes, one byte per cell, same (row, column) indexing as the fp64 arrays with row pitch
+  // `pitch` bytes: bits 0-1 class of a, bits 2-3 class of b, bits 4-5 class of D; class 0 = the value of a cell
+  // whose faces lie inside the ellipse (a = b = 1), 1 = outside (1/eps), 2 = anything else (read the array).
+  // All but O(M+N) cells are class 0 or 1, so the kernels stream one byte instead of three doubles.
+  unsigned char* cls;
   // neighbour r arrays as seen from this GPU (peer mapped), with their row pitch and extents
   double* nbr_r[4];
   int nbr_pitch[4];
@@ -84,6 +89,10 @@ struct RankCtx {
 constexpr int kTileX = 32;  // rows per stencil tile
 constexpr int kTileY = 64;  // columns per stencil tile
 
-inline size_t arena_bytes(const LocalBlock& b) { return kHeaderBytes + 8 * b.elems() * sizeof(double); }
+// 8 fp64 arrays + one byte per cell of coefficient classes (see RankCtx::cls)
+inline size_t arena_bytes(const LocalBlock& b) {
+  return kHeaderBytes + 8 * b.elems() * sizeof(double) + ((b.elems() + 255) / 256) * 256;
+}
+constexpr int kMapsPerVariant = 16;  // tensor maps per tile height (14 used)
 
 }  // namespace pb

@@ -19,9 +19,18 @@
 
 namespace pb {
 
-enum TmaMap : int { kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, kMapW, kMapP0, kMapP1, kMapR, kMapAp, kMapD };
+enum TmaMap : int {
+  kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, kMapW, kMapP0, kMapP1, kMapR, kMapAp, kMapD,
+  kMapClsAB,  // class bytes, (TX+2) rows x 80 bytes, box starts at a multiple of 16 columns
+  kMapClsC    // class bytes, TX rows x 80 bytes
+};
+constexpr int kClsBoxBytes = 80;  // 64 tile columns + ring + the up to 15 bytes in front of the aligned start
 
-template <int TX>
+// Shared-memory stage layout.  CC = "compressed coefficients": a, b and D are not streamed as fp64 boxes;
+// one class byte per cell (RankCtx::cls) selects 1, 1/eps or the respective diagonal constant, and only the
+// O(M+N) cells cut by the ellipse read the fp64 arrays.  82 instead of 112 B/node/iteration, 5 instead of 8
+// arrays in the streamed working set, and three pipeline stages instead of two.
+template <int TX, bool CC>
 struct TmaCfg {
   static constexpr int TY = kTileY;
   static constexpr int ER = TX + 2, EC = TY + 4;  // ring boxes start one column early: TMA wants 16-byte starts
@@ -30,20 +39,33 @@ struct TmaCfg {
   static constexpr int kABytes = (TX + 1) * TY * 8;
   static constexpr int kBBytes = TX * BC * 8;
   static constexpr int kTileBytes = TX * TY * 8;
-  static constexpr int kStageAB = 3 * kExtBytes + kABytes + kBBytes;
-  static constexpr int kStageC = 5 * kTileBytes;
+  static constexpr int kClsABBytes = ((ER * kClsBoxBytes + 127) / 128) * 128;
+  static constexpr int kClsCBytes = ((TX * kClsBoxBytes + 127) / 128) * 128;
+  // phase AB offsets
+  static constexpr int kOffR = 0;
+  static constexpr int kOffD = CC ? 0 : kExtBytes;  // unused with CC
+  static constexpr int kOffP = CC ? kExtBytes : 2 * kExtBytes;
+  static constexpr int kOffA = 3 * kExtBytes;       // unused with CC
+  static constexpr int kOffB = 3 * kExtBytes + kABytes;
+  static constexpr int kOffClsAB = 2 * kExtBytes;   // CC only
+  static constexpr int kStageAB = CC ? 2 * kExtBytes + kClsABBytes : 3 * kExtBytes + kABytes + kBBytes;
+  // phase C offsets: w, p, r, Ap, then D (fp64 box) or the class bytes
+  static constexpr int kOffCD = 4 * kTileBytes;
+  static constexpr int kStageC = CC ? 4 * kTileBytes + kClsCBytes : 5 * kTileBytes;
   static constexpr int kStageBytes = kStageAB > kStageC ? kStageAB : kStageC;
-  static constexpr int kStages = TX >= 32 ? 2 : 4;
+  static constexpr int kStages = CC ? (TX >= 32 ? 3 : 6) : (TX >= 32 ? 2 : 4);
   // transaction bytes = full boxes, out-of-bounds parts included
-  static constexpr uint32_t kTxAB = 3u * ER * EC * 8u + (uint32_t)kABytes + (uint32_t)kBBytes;
-  static constexpr uint32_t kTxC = 5u * (uint32_t)kTileBytes;
+  static constexpr uint32_t kTxAB = CC ? 2u * ER * EC * 8u + (uint32_t)(ER * kClsBoxBytes)
+                                       : 3u * ER * EC * 8u + (uint32_t)kABytes + (uint32_t)kBBytes;
+  static constexpr uint32_t kTxC = CC ? 4u * (uint32_t)kTileBytes + (uint32_t)(TX * kClsBoxBytes) : 5u * (uint32_t)kTileBytes;
   static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 128;
+  static_assert(kSmemBytes <= 227 * 1024, "stages do not fit into shared memory");
 };
 
-template <int TX, int DIV>
+template <int TX, int DIV, bool CC>
 __global__ void __launch_bounds__(kThreads, 1)
 pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints) {
-  using Cfg = TmaCfg<TX>;
+  using Cfg = TmaCfg<TX, CC>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
   __shared__ double s_red[80];
@@ -66,7 +88,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // s_dyn is declared __align__(128); deriving every stage pointer from it by plain pointer arithmetic keeps
   // the accesses in the shared address space (LDS/STS instead of generic LD/ST)
   unsigned char* const stage_base = s_dyn;
-  const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * 12;
+  const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * kMapsPerVariant;
 
   Control* ctl = c.ctl;
   const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + TX - 1) / TX;
@@ -88,6 +110,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const int norm = ctl->norm;
   const double h1h2 = c.g.h1h2;
   const StencilConsts K = make_stencil_consts(c.g);
+  // values behind the coefficient classes (same device functions as the assembly kernel -> same bits)
+  const double inv_eps = 1.0 / c.g.eps;
+  const double d_in = diag_from_faces(c.g, 1.0, 1.0, 1.0, 1.0), d_out = diag_from_faces(c.g, inv_eps, inv_eps, inv_eps, inv_eps);
+  const double y_in = __drcp_rn(d_in), y_out = __drcp_rn(d_out);
+  auto face_value = [&](unsigned int k, const double* cell) { return k == 0u ? 1.0 : (k == 1u ? inv_eps : __ldg(cell)); };
 
   // L2 policy per operand: what both phases of every iteration re-read (r, D, p) is kept, what is touched once
   // per iteration (a, b, w, Ap after its single use) is marked evict-first, so that on a working set around
@@ -163,10 +190,14 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (part1) {
         fence_proxy_async_smem();
         mbar_arrive_expect_tx(bar, Cfg::kTxAB);
-        tma_load_2d_hint(sb + Cfg::kExtBytes, maps + kMapDExt, x, y, bar, pol_keep);
-        tma_load_2d_hint(sb + 2 * Cfg::kExtBytes, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar, pol_keep);
-        tma_load_2d_hint(sb + 3 * Cfg::kExtBytes, maps + kMapA, x + 2, y + 1, bar, pol_stream);
-        tma_load_2d_hint(sb + 3 * Cfg::kExtBytes + Cfg::kABytes, maps + kMapB, x + 2, y + 1, bar, pol_stream);
+        tma_load_2d_hint(sb + Cfg::kOffP, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar, pol_keep);
+        if constexpr (CC) {
+          tma_load_2d_hint(sb + Cfg::kOffClsAB, maps + kMapClsAB, lj0 - 1, y, bar, pol_keep);  // lj0 - 1 = 64 * ty
+        } else {
+          tma_load_2d_hint(sb + Cfg::kOffD, maps + kMapDExt, x, y, bar, pol_keep);
+          tma_load_2d_hint(sb + Cfg::kOffA, maps + kMapA, x + 2, y + 1, bar, pol_stream);
+          tma_load_2d_hint(sb + Cfg::kOffB, maps + kMapB, x + 2, y + 1, bar, pol_stream);
+        }
       }
       if (part2) {
         // only a tile on a shared edge reads cells another GPU wrote since the phase-start fence
@@ -193,7 +224,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       tma_load_2d_hint(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar, pol_keep);
       tma_load_2d_hint(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar, pol_keep);
       tma_load_2d_hint(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar, pol_stream);
-      tma_load_2d_hint(sb + 4 * Cfg::kTileBytes, maps + kMapD, x, y, bar, pol_keep);
+      if constexpr (CC)
+        tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapClsC, lj0 - 1, y, bar, pol_keep);
+      else
+        tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapD, x, y, bar, pol_keep);
     }
     ++n_issued;
   };
@@ -265,10 +299,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       unsigned char* sb = wait_stage();
       if (!tma_ok) break;
       const double* s_r = reinterpret_cast<const double*>(sb);
-      const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kExtBytes);
-      double* s_p = reinterpret_cast<double*>(sb + 2 * Cfg::kExtBytes);
-      const double* s_a = reinterpret_cast<const double*>(sb + 3 * Cfg::kExtBytes);
-      const double* s_b = reinterpret_cast<const double*>(sb + 3 * Cfg::kExtBytes + Cfg::kABytes);
+      const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffD);
+      double* s_p = reinterpret_cast<double*>(sb + Cfg::kOffP);
+      const double* s_a = reinterpret_cast<const double*>(sb + Cfg::kOffA);
+      const double* s_b = reinterpret_cast<const double*>(sb + Cfg::kOffB);
+      const unsigned char* s_cls = sb + Cfg::kOffClsAB;  // CC: byte of ext cell (row, col) at row * 80 + 3 + col
       int li0, lj0;
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
@@ -281,9 +316,19 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         if (col < 0 || col >= cy + 2) return;
         const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
         if (!(row_in || col_in)) return;
-        const double v = fma(beta, s_p[e], div_var<DIV>(s_r[e], s_D[e]));
-        s_p[e] = v;
         const int li = li0 - 1 + row, lj = lj0 - 1 + col;
+        double z;
+        if constexpr (CC) {
+          const unsigned int kd = (s_cls[row * kClsBoxBytes + 3 + col] >> 4) & 3u;
+          if (kd == 2u)
+            z = div_var<DIV>(s_r[e], __ldg(&c.D[(size_t)li * S_pitch + (lj + kColOff)]));
+          else
+            z = div_known<DIV>(s_r[e], kd ? d_out : d_in, kd ? y_out : y_in);
+        } else {
+          z = div_var<DIV>(s_r[e], s_D[e]);
+        }
+        const double v = fma(beta, s_p[e], z);
+        s_p[e] = v;
         const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
         if ((row_in && col_in) || ring) pout[(size_t)li * S_pitch + (lj + kColOff)] = v;
       };
@@ -304,10 +349,19 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         auto ab_node = [&](int row, double& pc) {
           const double* s = s_p + row * EC + col + 1;
           pc = s[0];
-          const double v = stencil_value<DIV>(K, pc, s[-EC], s[EC], s[-1], s[1], s_a[(row - 1) * TY + (col - 1)],
-                                              s_a[row * TY + (col - 1)], s_b[(row - 1) * BC + (col - 1)],
-                                              s_b[(row - 1) * BC + col]);
-          c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
+          const size_t g = (size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff);
+          double a_c, a_ip, b_c, b_jp;
+          if constexpr (CC) {
+            const unsigned char* q = s_cls + row * kClsBoxBytes + 3 + col;
+            const unsigned int k_c = q[0], k_ip = q[kClsBoxBytes], k_jp = q[1];
+            a_c = face_value(k_c & 3u, c.a + g), a_ip = face_value(k_ip & 3u, c.a + g + S_pitch);
+            b_c = face_value((k_c >> 2) & 3u, c.b + g), b_jp = face_value((k_jp >> 2) & 3u, c.b + g + 1);
+          } else {
+            a_c = s_a[(row - 1) * TY + (col - 1)], a_ip = s_a[row * TY + (col - 1)];
+            b_c = s_b[(row - 1) * BC + (col - 1)], b_jp = s_b[(row - 1) * BC + col];
+          }
+          const double v = stencil_value<DIV>(K, pc, s[-EC], s[EC], s[-1], s[1], a_c, a_ip, b_c, b_jp);
+          c.Ap[g] = v;
           return v;
         };
         if (full) {
@@ -362,7 +416,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const double* s_p = reinterpret_cast<const double*>(sb + Cfg::kTileBytes);
       const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
       const double* s_Ap = reinterpret_cast<const double*>(sb + 3 * Cfg::kTileBytes);
-      const double* s_D = reinterpret_cast<const double*>(sb + 4 * Cfg::kTileBytes);
+      const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffCD);
+      const unsigned char* s_cls = sb + Cfg::kOffCD;  // CC: byte of node (row, col) at row * 80 + 4 + col
       int li0, lj0;
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
@@ -382,7 +437,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           c.w[g] = w_new;
         c.r[g] = r_new;
         d_out = __dsub_rn(w_new, w_old);
-        z_out = div_var<DIV>(r_new, s_D[e]);
+        if constexpr (CC) {
+          const unsigned int kd = (s_cls[row * kClsBoxBytes + 4 + col] >> 4) & 3u;
+          z_out = kd == 2u ? div_var<DIV>(r_new, __ldg(&c.D[g])) : div_known<DIV>(r_new, kd ? d_out : d_in, kd ? y_out : y_in);
+        } else {
+          z_out = div_var<DIV>(r_new, s_D[e]);
+        }
         r_out = r_new;
         if (li == 1 && c.nbr_r[kXm])
           c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
@@ -489,27 +549,32 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 }
 
 // ---------------------------------------------------------------------------------------------------
-template <int TX, int DIV>
+template <int TX, int DIV, bool CC>
 static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int l2_hints,
                                   cudaStream_t stream) {
-  const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV>;
-  const size_t smem = TmaCfg<TX>::kSmemBytes;
+  const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV, CC>;
+  const size_t smem = TmaCfg<TX, CC>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints};
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
 }
 
+template <int TX, bool CC>
+static cudaError_t launch_div(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int div, int l2_hints,
+                              cudaStream_t stream) {
+  if (div == kDivTrue) return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, stream);
+  if (div == kDivMarkstein) return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, stream);
+  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, stream);
+}
+
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
-                                  int l2_hints, cudaStream_t stream) {
-  if (tile_rows == 32) {
-    if (div == kDivTrue) return launch_variant<32, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 0, l2_hints, stream);
-    if (div == kDivMarkstein) return launch_variant<32, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 0, l2_hints, stream);
-    return launch_variant<32, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 0, l2_hints, stream);
-  }
-  if (div == kDivTrue) return launch_variant<16, kDivTrue>(d_ctxs, nvirt, ctas_per_rank, 1, l2_hints, stream);
-  if (div == kDivMarkstein) return launch_variant<16, kDivMarkstein>(d_ctxs, nvirt, ctas_per_rank, 1, l2_hints, stream);
-  return launch_variant<16, kDivRecip>(d_ctxs, nvirt, ctas_per_rank, 1, l2_hints, stream);
+                                  int l2_hints, bool compressed, cudaStream_t stream) {
+  if (tile_rows == 32)
+    return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, stream)
+                      : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, stream);
+  return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, stream)
+                    : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, stream);
 }
 
 // Debug / unit-test probe: one box load through a tensor map at (x, y) into shared memory, copied out to
@@ -575,6 +640,17 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
+static bool encode_u8(CUtensorMap* m, unsigned char* base, int rows, int pitch, int box_cols, int box_rows) {
+  if (!encode_fn()) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)pitch};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static bool encode(CUtensorMap* m, double* base, int rows, int pitch, int box_cols, int box_rows) {
   if (!encode_fn()) return false;
   const cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
@@ -602,6 +678,8 @@ bool build_tensor_maps(const RankCtx& h, int tile_rows, void* out12) {
   ok &= encode(m + kMapR, h.r, rows, P, TY, TX);
   ok &= encode(m + kMapAp, h.Ap, rows, P, TY, TX);
   ok &= encode(m + kMapD, h.D, rows, P, TY, TX);
+  ok &= encode_u8(m + kMapClsAB, h.cls, rows, P, kClsBoxBytes, TX + 2);
+  ok &= encode_u8(m + kMapClsC, h.cls, rows, P, kClsBoxBytes, TX);
   return ok;
 }
 

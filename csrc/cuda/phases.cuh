@@ -80,6 +80,14 @@ __device__ __forceinline__ double div_var(double r, double D) {
   return D != 0.0 ? z : 0.0;
 }
 
+// z = r / D when RN(1/D) is already known (D is one of the two diagonal constants of the coefficient classes).
+template <int DIV>
+__device__ __forceinline__ double div_known(double r, double D, double y) {
+  if (DIV == kDivTrue) return r / D;
+  const double q = __dmul_rn(r, y);
+  return fma(fma(-q, D, r), y, q);
+}
+
 // (A p) at one node, association of the reference (S4:526-535).
 template <int DIV>
 __device__ __forceinline__ double stencil_value(const StencilConsts& k, double pc, double pim, double pip, double pjm,

@@ -24,6 +24,7 @@ struct SolveOptions {
   int exact_div = 2;        // stencil divisions: 0 reciprocal multiply, 1 true division, 2 Markstein (= 1 bitwise)
   int ctas_per_sm = 0;      // 0 = auto
   int error_report = 1;
+  int compressed = 1;       // TMA kernel: coefficient classes (1 byte/cell) instead of streaming a, b, D
   int l2_hints = 0;         // TMA loads carry L2 eviction priorities (helps ~2 % when the working set ~ L2 size)
   int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages) or 16 (4 stages); 0 = auto
   double watchdog_s = 0.0;  // 0 = default (20 s)

@@ -30,7 +30,7 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   }
   if (tma)
     PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact,
-                                        opt.l2_hints, stream));
+                                        opt.l2_hints, opt.compressed != 0, stream));
   else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;

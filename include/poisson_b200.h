@@ -119,7 +119,7 @@ typedef struct pb_solve_options {
   int tile_rows;      /* TMA persistent kernel: 32 (2 pipeline stages) or 16 (4 stages); 0 = auto */
   double watchdog_s;  /* 0 = default (20 s): device-side waits give up after this long */
   int l2_hints;       /* 1: TMA loads carry L2 eviction priorities (keep r, D, p; stream a, b, w, Ap) */
-  int reserved;
+  int full_coefficients; /* 1: stream a, b, D as fp64 boxes instead of the 1-byte coefficient classes (A/B testing) */
 } pb_solve_options;
 
 int pb_cuda_device_count(void);

@@ -77,7 +77,7 @@ class SolveOptions(C.Structure):
         ("tile_rows", C.c_int),
         ("watchdog_s", C.c_double),
         ("l2_hints", C.c_int),
-        ("reserved", C.c_int),
+        ("full_coefficients", C.c_int),
     ]
 
 

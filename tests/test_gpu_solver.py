@@ -188,3 +188,30 @@ def test_apply_A_dot_operator_matches_fp32_free_reference(native):
     assert torch.allclose(Ap.cpu()[I, J], Aph[I, J], rtol=1e-13, atol=1e-9)
     assert dot.item() == pytest.approx(s_cpu * h1 * h2, rel=1e-12)
     s.close()
+
+
+@pytest.mark.parametrize("pg", [(1, 1), (2, 2), (3, 1)])
+@pytest.mark.parametrize("tile_rows", [32, 16])
+def test_coefficient_classes_are_bit_identical_to_streamed_coefficients(pg, tile_rows):
+    """The 1-byte class path (a, b, D from {1, 1/eps, constants} or a rare array read) must give the same bits as
+    streaming the fp64 coefficient boxes."""
+    for grid in [(96, 200), (400, 600)]:
+        s = _solver(*grid, *pg)
+        ra = s.solve(tile_rows=tile_rows, full_coefficients=True)
+        wa = s.solution_host().clone()
+        rb = s.solve(tile_rows=tile_rows)
+        wb = s.solution_host()
+        assert ra["iters"] == rb["iters"]
+        assert torch.equal(wa, wb)
+        s.close()
+
+
+def test_class_bytes_match_arrays(native):
+    s = _solver(200, 300).finalize()
+    s.step("assemble")
+    torch.cuda.synchronize()
+    a, b, D = s.array("a"), s.array("b"), s.array("D")
+    inv_eps = 1.0 / max(2.0 / 200, 1.2 / 300) ** 2
+    frac_cut = ((a != 1.0) & (a != inv_eps)).double().mean().item()
+    assert 0 < frac_cut < 0.02  # only the faces cut by the ellipse carry a blended coefficient
+    s.close()
