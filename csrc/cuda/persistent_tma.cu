@@ -4,33 +4,36 @@
 // phase is a software pipeline over the CTA's tiles: one elected thread issues `cp.async.bulk.tensor.2d`
 // loads for tile j+S-1 (all operand boxes of the tile land in one shared-memory stage and complete on one
 // mbarrier) while all warps compute tile j out of shared memory.  A stage holds
-//     phase AB: r, D, p_old boxes of (TX+2) x (TY+4) (tile + ring; one more column on each side because a
-//               box must start on a 16-byte boundary), a box (TX+1) x TY, b box TX x (TY+2)
-//     phase C : w, p, r, Ap, D boxes of TX x TY
-// so one SM keeps S-1 complete tiles (45-88 KB each) in flight without spending registers on it, which is
+//     phase AB: r, p_old boxes of (TX+2) x (TY+4) (tile + ring; one more column on each side because a box
+//               must start on a 16-byte boundary) and, for tiles with non-constant coefficients, the D box
+//               of the same shape, the a box (TX+1) x TY and the b box TX x (TY+2)
+//     phase C : w, p, r, Ap boxes of TX x TY (+ the D box for tiles with non-constant coefficients)
+// so one SM keeps S-1 complete tiles (up to 88 KB each) in flight without spending registers on it, which is
 // what a bandwidth-bound fp64 stencil needs on a part with ~40 KB/SM of latency-bandwidth product.
 // The TMA unit also does the address generation for the misaligned ring boxes and zero-fills the part of
 // a box that lies outside the array (partial tiles at the block edge).
 //
+// Coefficient classes (CC = true, the default): a and b take the value 1 on faces inside the ellipse, 1/eps
+// outside, and something else only on the O(M+N) faces the ellipse cuts; D follows.  The assembly kernel
+// stores one class byte per cell; at launch every CTA classifies its tiles once.  A tile whose cells (ring
+// included) are all "inside" or all "outside" needs no coefficient boxes at all -- a, b, D are CTA-uniform
+// constants -- which removes 24 of the 112 bytes per node and iteration for all but the few tiles crossed by
+// the ellipse or touching the boundary of Omega; those keep the full fp64 boxes.  Values are selected, never
+// recomputed, so the results are bit-identical to streaming the coefficient arrays (tests compare them).
+//
 // Replaces the same reference pieces as persistent.cu (S4:846-942, kernels S4:507-676).
+#include <type_traits>
+
 #include "launch.h"
 #include "phases.cuh"
 #include "tma_utils.cuh"
 
 namespace pb {
 
-enum TmaMap : int {
-  kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, kMapW, kMapP0, kMapP1, kMapR, kMapAp, kMapD,
-  kMapClsAB,  // class bytes, (TX+2) rows x 80 bytes, box starts at a multiple of 16 columns
-  kMapClsC    // class bytes, TX rows x 80 bytes
-};
-constexpr int kClsBoxBytes = 80;  // 64 tile columns + ring + the up to 15 bytes in front of the aligned start
+enum TmaMap : int { kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, kMapW, kMapP0, kMapP1, kMapR, kMapAp, kMapD };
+constexpr int kMaxTileClass = 1024;  // tiles per CTA whose class is cached in shared memory (more: treated as mixed)
 
-// Shared-memory stage layout.  CC = "compressed coefficients": a, b and D are not streamed as fp64 boxes;
-// one class byte per cell (RankCtx::cls) selects 1, 1/eps or the respective diagonal constant, and only the
-// O(M+N) cells cut by the ellipse read the fp64 arrays.  82 instead of 112 B/node/iteration, 5 instead of 8
-// arrays in the streamed working set, and three pipeline stages instead of two.
-template <int TX, bool CC>
+template <int TX>
 struct TmaCfg {
   static constexpr int TY = kTileY;
   static constexpr int ER = TX + 2, EC = TY + 4;  // ring boxes start one column early: TMA wants 16-byte starts
@@ -39,25 +42,19 @@ struct TmaCfg {
   static constexpr int kABytes = (TX + 1) * TY * 8;
   static constexpr int kBBytes = TX * BC * 8;
   static constexpr int kTileBytes = TX * TY * 8;
-  static constexpr int kClsABBytes = ((ER * kClsBoxBytes + 127) / 128) * 128;
-  static constexpr int kClsCBytes = ((TX * kClsBoxBytes + 127) / 128) * 128;
-  // phase AB offsets
-  static constexpr int kOffR = 0;
-  static constexpr int kOffD = CC ? 0 : kExtBytes;  // unused with CC
-  static constexpr int kOffP = CC ? kExtBytes : 2 * kExtBytes;
-  static constexpr int kOffA = 3 * kExtBytes;       // unused with CC
+  // phase AB: r | p | D | a | b      phase C: w | p | r | Ap | D
+  static constexpr int kOffR = 0, kOffP = kExtBytes, kOffD = 2 * kExtBytes, kOffA = 3 * kExtBytes;
   static constexpr int kOffB = 3 * kExtBytes + kABytes;
-  static constexpr int kOffClsAB = 2 * kExtBytes;   // CC only
-  static constexpr int kStageAB = CC ? 2 * kExtBytes + kClsABBytes : 3 * kExtBytes + kABytes + kBBytes;
-  // phase C offsets: w, p, r, Ap, then D (fp64 box) or the class bytes
   static constexpr int kOffCD = 4 * kTileBytes;
-  static constexpr int kStageC = CC ? 4 * kTileBytes + kClsCBytes : 5 * kTileBytes;
+  static constexpr int kStageAB = 3 * kExtBytes + kABytes + kBBytes;
+  static constexpr int kStageC = 5 * kTileBytes;
   static constexpr int kStageBytes = kStageAB > kStageC ? kStageAB : kStageC;
-  static constexpr int kStages = CC ? (TX >= 32 ? 3 : 6) : (TX >= 32 ? 2 : 4);
+  static constexpr int kStages = TX >= 32 ? 2 : 4;
   // transaction bytes = full boxes, out-of-bounds parts included
-  static constexpr uint32_t kTxAB = CC ? 2u * ER * EC * 8u + (uint32_t)(ER * kClsBoxBytes)
-                                       : 3u * ER * EC * 8u + (uint32_t)kABytes + (uint32_t)kBBytes;
-  static constexpr uint32_t kTxC = CC ? 4u * (uint32_t)kTileBytes + (uint32_t)(TX * kClsBoxBytes) : 5u * (uint32_t)kTileBytes;
+  static constexpr uint32_t kTxABCore = 2u * ER * EC * 8u;                                       // r, p
+  static constexpr uint32_t kTxABCoef = 1u * ER * EC * 8u + (uint32_t)kABytes + (uint32_t)kBBytes;  // D, a, b
+  static constexpr uint32_t kTxCCore = 4u * (uint32_t)kTileBytes;                                // w, p, r, Ap
+  static constexpr uint32_t kTxCCoef = (uint32_t)kTileBytes;                                     // D
   static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 128;
   static_assert(kSmemBytes <= 227 * 1024, "stages do not fit into shared memory");
 };
@@ -65,11 +62,12 @@ struct TmaCfg {
 template <int TX, int DIV, bool CC>
 __global__ void __launch_bounds__(kThreads, 1)
 pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints) {
-  using Cfg = TmaCfg<TX, CC>;
+  using Cfg = TmaCfg<TX>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
   __shared__ double s_red[80];
   __shared__ __align__(8) uint64_t s_bar[S];
+  __shared__ unsigned char s_tclass[kMaxTileClass];
   extern __shared__ __align__(128) unsigned char s_dyn[];
 
   const int vrank = blockIdx.x / ctas_per_rank;
@@ -112,13 +110,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const StencilConsts K = make_stencil_consts(c.g);
   // values behind the coefficient classes (same device functions as the assembly kernel -> same bits)
   const double inv_eps = 1.0 / c.g.eps;
-  const double d_in = diag_from_faces(c.g, 1.0, 1.0, 1.0, 1.0), d_out = diag_from_faces(c.g, inv_eps, inv_eps, inv_eps, inv_eps);
-  const double y_in = __drcp_rn(d_in), y_out = __drcp_rn(d_out);
-  auto face_value = [&](unsigned int k, const double* cell) { return k == 0u ? 1.0 : (k == 1u ? inv_eps : __ldg(cell)); };
+  const double diag_in = diag_from_faces(c.g, 1.0, 1.0, 1.0, 1.0);
+  const double diag_out = diag_from_faces(c.g, inv_eps, inv_eps, inv_eps, inv_eps);
+  const double rcp_in = __drcp_rn(diag_in), rcp_out = __drcp_rn(diag_out);
 
   // L2 policy per operand: what both phases of every iteration re-read (r, D, p) is kept, what is touched once
-  // per iteration (a, b, w, Ap after its single use) is marked evict-first, so that on a working set around
-  // the L2 size (4096^2 over 8 GPUs: 134 MB per GPU vs 126 MB) the re-read part stays resident.
+  // per iteration (a, b, w, Ap after its single use) is marked evict-first (optional).
   const uint64_t pol_keep = l2_hints ? kL2EvictLast : kL2EvictNormal;
   const uint64_t pol_stream = l2_hints ? kL2EvictFirst : kL2EvictNormal;
 
@@ -144,6 +141,28 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         last_halo_j = j;
     }
   }
+  // Tile classes: 0 = every cell of the tile and its ring is "inside" (a = b = 1, D = diag_in), 1 = all
+  // "outside" (1/eps, diag_out), 2 = mixed (full coefficient boxes).  One pass over the class bytes per launch.
+  if constexpr (CC) {
+    for (int j = 0; j < nmine && j < kMaxTileClass; ++j) {
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+      bool all_in = true, all_out = true;
+      for (int e = threadIdx.x; e < (cx + 2) * (cy + 2); e += kThreads) {
+        const int row = e / (cy + 2), col = e - row * (cy + 2);
+        if ((row == 0 || row == cx + 1) && (col == 0 || col == cy + 1)) continue;
+        const unsigned int b = c.cls[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)];
+        all_in = all_in && (b == 0x00u);
+        all_out = all_out && (b == 0x15u);
+      }
+      const int in = __syncthreads_and(all_in ? 1 : 0), out = __syncthreads_and(all_out ? 1 : 0);
+      if (threadIdx.x == 0) s_tclass[j] = in ? 0 : (out ? 1 : 2);
+    }
+    __syncthreads();
+  }
+  auto tile_mode = [&](int j) -> int { return (CC && j < kMaxTileClass) ? (int)s_tclass[j] : 2; };
+
   // Halo completion counters (see ctx.h): value at launch, and by how much one phase C of the neighbour
   // raises ours (= the number of its tiles along the shared edge).
   unsigned long long halo_base[4];
@@ -179,7 +198,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     return waited;
   };
   // Phase-AB loads of tile j into stage `st`.  part 1 = everything that does not depend on the other CTAs'
-  // phase C (D, p, a, b; arms the barrier with the full byte count), part 2 = the r box.
+  // phase C (p and, for mixed tiles, D, a, b; arms the barrier with the full byte count), part 2 = the r box.
   auto issue_ab_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2, long long rounds) {
     if (threadIdx.x == 0) {
       int li0, lj0;
@@ -188,12 +207,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       uint64_t* bar = &s_bar[st];
       const int x = kColOff + lj0 - 2, y = li0 - 1;  // even column: 16-byte aligned box start
       if (part1) {
+        const bool coef = tile_mode(j) == 2;
         fence_proxy_async_smem();
-        mbar_arrive_expect_tx(bar, Cfg::kTxAB);
+        mbar_arrive_expect_tx(bar, Cfg::kTxABCore + (coef ? Cfg::kTxABCoef : 0u));
         tma_load_2d_hint(sb + Cfg::kOffP, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar, pol_keep);
-        if constexpr (CC) {
-          tma_load_2d_hint(sb + Cfg::kOffClsAB, maps + kMapClsAB, lj0 - 1, y, bar, pol_keep);  // lj0 - 1 = 64 * ty
-        } else {
+        if (coef) {
           tma_load_2d_hint(sb + Cfg::kOffD, maps + kMapDExt, x, y, bar, pol_keep);
           tma_load_2d_hint(sb + Cfg::kOffA, maps + kMapA, x + 2, y + 1, bar, pol_stream);
           tma_load_2d_hint(sb + Cfg::kOffB, maps + kMapB, x + 2, y + 1, bar, pol_stream);
@@ -202,7 +220,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (part2) {
         // only a tile on a shared edge reads cells another GPU wrote since the phase-start fence
         if (has_nbr && wait_halo(li0, lj0, rounds)) fence_proxy_async();  // acquired generic-proxy stores -> TMA read
-        tma_load_2d_hint(sb, maps + kMapRExt, x, y, bar, pol_keep);
+        tma_load_2d_hint(sb + Cfg::kOffR, maps + kMapRExt, x, y, bar, pol_keep);
       }
     }
   };
@@ -217,17 +235,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const unsigned int st = n_issued % S;
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
+      const bool coef = tile_mode(j) == 2;
       fence_proxy_async_smem();
-      mbar_arrive_expect_tx(bar, Cfg::kTxC);
+      mbar_arrive_expect_tx(bar, Cfg::kTxCCore + (coef ? Cfg::kTxCCoef : 0u));
       const int x = kColOff + lj0, y = li0;
       tma_load_2d_hint(sb, maps + kMapW, x, y, bar, pol_stream);
       tma_load_2d_hint(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar, pol_keep);
       tma_load_2d_hint(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar, pol_keep);
       tma_load_2d_hint(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar, pol_stream);
-      if constexpr (CC)
-        tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapClsC, lj0 - 1, y, bar, pol_keep);
-      else
-        tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapD, x, y, bar, pol_keep);
+      if (coef) tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapD, x, y, bar, pol_keep);
     }
     ++n_issued;
   };
@@ -298,79 +314,72 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (j + S - 1 < nmine) issue_ab(j + S - 1, cur, k - 1);
       unsigned char* sb = wait_stage();
       if (!tma_ok) break;
-      const double* s_r = reinterpret_cast<const double*>(sb);
-      const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffD);
+      const double* s_r = reinterpret_cast<const double*>(sb + Cfg::kOffR);
       double* s_p = reinterpret_cast<double*>(sb + Cfg::kOffP);
+      const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffD);
       const double* s_a = reinterpret_cast<const double*>(sb + Cfg::kOffA);
       const double* s_b = reinterpret_cast<const double*>(sb + Cfg::kOffB);
-      const unsigned char* s_cls = sb + Cfg::kOffClsAB;  // CC: byte of ext cell (row, col) at row * 80 + 3 + col
       int li0, lj0;
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
-      // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory.
-      //    Full tiles take fixed-trip loops that the compiler unrolls, so the dependent fp64 chains of several
-      //    cells are in flight per thread (16 warps per SM do not hide them otherwise).
       const bool full = (cx == TX) && (cy == TY);
-      auto ab_cell = [&](int e) {
-        const int row = e / EC, col = e - row * EC - 1;  // col 0 = left ring column of the tile
-        if (col < 0 || col >= cy + 2) return;
-        const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
-        if (!(row_in || col_in)) return;
-        const int li = li0 - 1 + row, lj = lj0 - 1 + col;
-        double z;
-        if constexpr (CC) {
-          const unsigned int kd = (s_cls[row * kClsBoxBytes + 3 + col] >> 4) & 3u;
-          if (kd == 2u)
-            z = div_var<DIV>(s_r[e], __ldg(&c.D[(size_t)li * S_pitch + (lj + kColOff)]));
-          else
-            z = div_known<DIV>(s_r[e], kd ? d_out : d_in, kd ? y_out : y_in);
-        } else {
-          z = div_var<DIV>(s_r[e], s_D[e]);
-        }
-        const double v = fma(beta, s_p[e], z);
-        s_p[e] = v;
-        const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
-        if ((row_in && col_in) || ring) pout[(size_t)li * S_pitch + (lj + kColOff)] = v;
-      };
-      if (full) {
-        constexpr int kCells = (TX + 2) * EC;
+      const int tmode = tile_mode(j);  // CTA-uniform
+      const double cf = tmode == 1 ? inv_eps : 1.0;  // uniform tiles: every face coefficient
+      const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
+
+      // The two halves of the phase on one tile.  `uniform` is a compile-time tag, so the constant-coefficient
+      // path carries no shared-memory coefficient loads and the mixed path no selects.
+      auto run_tile = [&](auto uniform) {
+        constexpr bool U = decltype(uniform)::value;
+        // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory.  Full tiles take
+        //    fixed-trip loops that the compiler unrolls, so the dependent fp64 chains of several cells are in
+        //    flight per thread (16 warps per SM do not hide them otherwise).
+        auto ab_cell = [&](int e) {
+          const int row = e / EC, col = e - row * EC - 1;  // col 0 = left ring column of the tile
+          if (col < 0 || col >= cy + 2) return;
+          const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
+          if (!(row_in || col_in)) return;
+          const double z = U ? div_known<DIV>(s_r[e], dg, rc) : div_var<DIV>(s_r[e], s_D[e]);
+          const double v = fma(beta, s_p[e], z);
+          s_p[e] = v;
+          const int li = li0 - 1 + row, lj = lj0 - 1 + col;
+          const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
+          if ((row_in && col_in) || ring) pout[(size_t)li * S_pitch + (lj + kColOff)] = v;
+        };
+        if (full) {
+          constexpr int kCells = (TX + 2) * EC;
 #pragma unroll
-        for (int k = 0; k < (kCells + kThreads - 1) / kThreads; ++k) {
-          const int e = threadIdx.x + k * kThreads;
-          if (e < kCells) ab_cell(e);
+          for (int q = 0; q < (kCells + kThreads - 1) / kThreads; ++q) {
+            const int e = threadIdx.x + q * kThreads;
+            if (e < kCells) ab_cell(e);
+          }
+        } else {
+          for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) ab_cell(e);
         }
-      } else {
-        for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) ab_cell(e);
-      }
-      __syncthreads();
-      // 2. Ap = A p_new on the owned nodes of the tile
-      {
+        __syncthreads();
+        // 2. Ap = A p_new on the owned nodes of the tile
         const int col = threadIdx.x % TY + 1;
         auto ab_node = [&](int row, double& pc) {
           const double* s = s_p + row * EC + col + 1;
           pc = s[0];
-          const size_t g = (size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff);
           double a_c, a_ip, b_c, b_jp;
-          if constexpr (CC) {
-            const unsigned char* q = s_cls + row * kClsBoxBytes + 3 + col;
-            const unsigned int k_c = q[0], k_ip = q[kClsBoxBytes], k_jp = q[1];
-            a_c = face_value(k_c & 3u, c.a + g), a_ip = face_value(k_ip & 3u, c.a + g + S_pitch);
-            b_c = face_value((k_c >> 2) & 3u, c.b + g), b_jp = face_value((k_jp >> 2) & 3u, c.b + g + 1);
+          if constexpr (U) {
+            a_c = a_ip = b_c = b_jp = cf;
           } else {
             a_c = s_a[(row - 1) * TY + (col - 1)], a_ip = s_a[row * TY + (col - 1)];
             b_c = s_b[(row - 1) * BC + (col - 1)], b_jp = s_b[(row - 1) * BC + col];
           }
           const double v = stencil_value<DIV>(K, pc, s[-EC], s[EC], s[-1], s[1], a_c, a_ip, b_c, b_jp);
-          c.Ap[g] = v;
+          c.Ap[(size_t)(li0 - 1 + row) * S_pitch + (lj0 - 1 + col + kColOff)] = v;
           return v;
         };
         if (full) {
           constexpr int kPer = TX / (kThreads / TY);  // nodes per thread
           double v[kPer], pc[kPer];
 #pragma unroll
-          for (int k = 0; k < kPer; ++k) v[k] = ab_node(threadIdx.x / TY + 1 + k * (kThreads / TY), pc[k]);
+          for (int q = 0; q < kPer; ++q) v[q] = ab_node(threadIdx.x / TY + 1 + q * (kThreads / TY), pc[q]);
 #pragma unroll
-          for (int k = 0; k < kPer; ++k) acc_ab = fma(v[k], pc[k], acc_ab);  // same order as the generic loop
+          for (int q = 0; q < kPer; ++q) acc_ab = fma(v[q], pc[q], acc_ab);  // same order as the generic loop
         } else if (col <= cy) {
           for (int row = threadIdx.x / TY + 1; row <= cx; row += kThreads / TY) {
             double pc;
@@ -378,7 +387,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
             acc_ab = fma(v, pc, acc_ab);
           }
         }
-      }
+      };
+      if (tmode != 2)
+        run_tile(std::true_type{});
+      else
+        run_tile(std::false_type{});
       __syncthreads();  // stage free
       ++n_consumed;
     }
@@ -417,58 +430,61 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
       const double* s_Ap = reinterpret_cast<const double*>(sb + 3 * Cfg::kTileBytes);
       const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffCD);
-      const unsigned char* s_cls = sb + Cfg::kOffCD;  // CC: byte of node (row, col) at row * 80 + 4 + col
       int li0, lj0;
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
       const int col = threadIdx.x % TY;
       const bool full = (cx == TX) && (cy == TY);
-      // loads and arithmetic of one node; stores and halo stores included
-      auto c_node = [&](int row, double& d_out, double& z_out, double& r_out) {
-        const int e = row * TY + col;
-        const int li = li0 + row, lj = lj0 + col;
-        const size_t g = (size_t)li * S_pitch + (lj + kColOff);
-        const double w_old = s_w[e];
-        const double w_new = fma(alpha, s_p[e], w_old);
-        const double r_new = fma(-alpha, s_Ap[e], s_r[e]);
-        if (l2_hints)
-          __stcs(&c.w[g], w_new);  // streaming store: w is not read again before the next iteration's phase C
-        else
-          c.w[g] = w_new;
-        c.r[g] = r_new;
-        d_out = __dsub_rn(w_new, w_old);
-        if constexpr (CC) {
-          const unsigned int kd = (s_cls[row * kClsBoxBytes + 4 + col] >> 4) & 3u;
-          z_out = kd == 2u ? div_var<DIV>(r_new, __ldg(&c.D[g])) : div_known<DIV>(r_new, kd ? d_out : d_in, kd ? y_out : y_in);
-        } else {
-          z_out = div_var<DIV>(r_new, s_D[e]);
+      const int tmode = tile_mode(j);  // CTA-uniform
+      const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
+      auto run_tile = [&](auto uniform) {
+        constexpr bool U = decltype(uniform)::value;
+        // loads and arithmetic of one node; stores and halo stores included
+        auto c_node = [&](int row, double& dw, double& z, double& rn) {
+          const int e = row * TY + col;
+          const int li = li0 + row, lj = lj0 + col;
+          const size_t g = (size_t)li * S_pitch + (lj + kColOff);
+          const double w_old = s_w[e];
+          const double w_new = fma(alpha, s_p[e], w_old);
+          const double r_new = fma(-alpha, s_Ap[e], s_r[e]);
+          if (l2_hints)
+            __stcs(&c.w[g], w_new);  // streaming store: w is not read again before the next iteration's phase C
+          else
+            c.w[g] = w_new;
+          c.r[g] = r_new;
+          dw = __dsub_rn(w_new, w_old);
+          z = U ? div_known<DIV>(r_new, dg, rc) : div_var<DIV>(r_new, s_D[e]);
+          rn = r_new;
+          if (li == 1 && c.nbr_r[kXm])
+            c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
+          if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
+          if (lj == 1 && c.nbr_r[kYm])
+            c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
+          if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+        };
+        if (full) {
+          constexpr int kPer = TX / (kThreads / TY);
+          double dw[kPer], z[kPer], rn[kPer];
+#pragma unroll
+          for (int q = 0; q < kPer; ++q) c_node(threadIdx.x / TY + q * (kThreads / TY), dw[q], z[q], rn[q]);
+#pragma unroll
+          for (int q = 0; q < kPer; ++q) {
+            acc_d = fma(dw[q], dw[q], acc_d);
+            acc_zr = fma(z[q], rn[q], acc_zr);
+          }
+        } else if (col < cy) {
+          for (int row = threadIdx.x / TY; row < cx; row += kThreads / TY) {
+            double dw, z, rn;
+            c_node(row, dw, z, rn);
+            acc_d = fma(dw, dw, acc_d);
+            acc_zr = fma(z, rn, acc_zr);
+          }
         }
-        r_out = r_new;
-        if (li == 1 && c.nbr_r[kXm])
-          c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
-        if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
-        if (lj == 1 && c.nbr_r[kYm])
-          c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
-        if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
       };
-      if (full) {
-        constexpr int kPer = TX / (kThreads / TY);
-        double d[kPer], z[kPer], rn[kPer];
-#pragma unroll
-        for (int k = 0; k < kPer; ++k) c_node(threadIdx.x / TY + k * (kThreads / TY), d[k], z[k], rn[k]);
-#pragma unroll
-        for (int k = 0; k < kPer; ++k) {
-          acc_d = fma(d[k], d[k], acc_d);
-          acc_zr = fma(z[k], rn[k], acc_zr);
-        }
-      } else if (col < cy) {
-        for (int row = threadIdx.x / TY; row < cx; row += kThreads / TY) {
-          double d, z, rn;
-          c_node(row, d, z, rn);
-          acc_d = fma(d, d, acc_d);
-          acc_zr = fma(z, rn, acc_zr);
-        }
-      }
+      if (tmode != 2)
+        run_tile(std::true_type{});
+      else
+        run_tile(std::false_type{});
       if (has_nbr && j <= last_halo_j) {
         pushed[kXm] += (li0 == 1), pushed[kXp] += (li0 + cx - 1 == c.nx);
         pushed[kYm] += (lj0 == 1), pushed[kYp] += (lj0 + cy - 1 == c.ny);
@@ -487,7 +503,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       ++n_consumed;
     }
     if (!tma_ok) break;
-    // Prefetch for the next phase AB, part 1: D, a, b are constant and p_new (buffer cur^1, ring included)
+    // Prefetch for the next phase AB, part 1: coefficients are constant and p_new (buffer cur^1, ring included)
     // was completed before the previous reduction.  The r box waits for the reduction below, because its
     // ring cells are written by other CTAs / GPUs during this very phase.
     const unsigned int pre_base = n_issued;
@@ -553,7 +569,7 @@ template <int TX, int DIV, bool CC>
 static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int l2_hints,
                                   cudaStream_t stream) {
   const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV, CC>;
-  const size_t smem = TmaCfg<TX, CC>::kSmemBytes;
+  const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints};
@@ -640,17 +656,6 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-static bool encode_u8(CUtensorMap* m, unsigned char* base, int rows, int pitch, int box_cols, int box_rows) {
-  if (!encode_fn()) return false;
-  const cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)pitch};
-  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  return encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 static bool encode(CUtensorMap* m, double* base, int rows, int pitch, int box_cols, int box_rows) {
   if (!encode_fn()) return false;
   const cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
@@ -678,8 +683,6 @@ bool build_tensor_maps(const RankCtx& h, int tile_rows, void* out12) {
   ok &= encode(m + kMapR, h.r, rows, P, TY, TX);
   ok &= encode(m + kMapAp, h.Ap, rows, P, TY, TX);
   ok &= encode(m + kMapD, h.D, rows, P, TY, TX);
-  ok &= encode_u8(m + kMapClsAB, h.cls, rows, P, kClsBoxBytes, TX + 2);
-  ok &= encode_u8(m + kMapClsC, h.cls, rows, P, kClsBoxBytes, TX);
   return ok;
 }
 
