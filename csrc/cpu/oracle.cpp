@@ -174,7 +174,10 @@ void cpu_assemble_local(const Grid& g, const LocalBlock& blk, double* a, double*
   const int nthreads = clamp_threads(threads);
   (void)nthreads;
   // a, b on the block plus its ring, from global indices (S4:154-178); D, rhs on block plus ring, with
-  // the Dirichlet ring (global boundary) set to D=1, rhs=0 so that r/D is 0 there.
+  // the Dirichlet ring (global boundary) set to rhs = 0 and D = the diagonal of a cell far outside the
+  // ellipse (any non-zero value would do: it only ever divides zero), so that r/D is 0 there.
+  const double inv_eps = 1.0 / g.eps;
+  const double d_ring = diag_from_faces(g, inv_eps, inv_eps, inv_eps, inv_eps);
 #pragma omp parallel for num_threads(nthreads) schedule(static)
   for (int li = 0; li <= blk.nx + 1; ++li)
     for (int lj = 0; lj <= blk.ny + 1; ++lj) {
@@ -183,7 +186,7 @@ void cpu_assemble_local(const Grid& g, const LocalBlock& blk, double* a, double*
       a[c] = coef_a(g, gi, gj);
       b[c] = coef_b(g, gi, gj);
       const bool interior = gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1;
-      D[c] = interior ? diag_value(g, gi, gj) : 1.0;
+      D[c] = interior ? diag_value(g, gi, gj) : d_ring;
       rhs[c] = interior ? rhs_value(g, gi, gj) : 0.0;
     }
 }

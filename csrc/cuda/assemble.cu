@@ -26,7 +26,10 @@ __global__ void __launch_bounds__(256) assemble_kernel(const RankCtx* __restrict
     c.a[g] = a_c;
     c.b[g] = b_c;
     const bool interior = gi >= 1 && gi <= c.g.M - 1 && gj >= 1 && gj <= c.g.N - 1;
-    double d = 1.0, rhs = 0.0;
+    // Cells on the boundary of Omega (Dirichlet, part of the ring only): r is 0 there for ever, so D only ever
+    // divides zero.  It gets the diagonal of a cell far outside the ellipse, which keeps the tiles along the
+    // boundary of Omega in the constant-coefficient class.
+    double d = d_out, rhs = 0.0;
     if (interior) {
       d = diag_from_faces(c.g, a_c, coef_a(c.g, gi + 1, gj), b_c, coef_b(c.g, gi, gj + 1));
       rhs = rhs_value(c.g, gi, gj);

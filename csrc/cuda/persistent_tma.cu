@@ -331,30 +331,34 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       // path carries no shared-memory coefficient loads and the mixed path no selects.
       auto run_tile = [&](auto uniform) {
         constexpr bool U = decltype(uniform)::value;
-        // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory.  Full tiles take
-        //    fixed-trip loops that the compiler unrolls, so the dependent fp64 chains of several cells are in
-        //    flight per thread (16 warps per SM do not hide them otherwise).
-        auto ab_cell = [&](int e) {
-          const int row = e / EC, col = e - row * EC - 1;  // col 0 = left ring column of the tile
-          if (col < 0 || col >= cy + 2) return;
-          const bool row_in = row >= 1 && row <= cx, col_in = col >= 1 && col <= cy;
-          if (!(row_in || col_in)) return;
+        // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory.  The owned cells
+        //    map to threads without any division or validity test (4 cells per thread, unrolled for full
+        //    tiles so that their dependent fp64 chains overlap); the ring (top, bottom, left, right: at most
+        //    2 TY + 2 TX cells) is one extra cell for the first 192 threads.  A cell of shared-memory row `er`,
+        //    tile column `ec` (0 = left ring) sits at er * EC + ec + 1 (the box starts one column early).
+        auto p_cell = [&](int er, int ec, bool store) {
+          const int e = er * EC + ec + 1;
           const double z = U ? div_known<DIV>(s_r[e], dg, rc) : div_var<DIV>(s_r[e], s_D[e]);
           const double v = fma(beta, s_p[e], z);
           s_p[e] = v;
-          const int li = li0 - 1 + row, lj = lj0 - 1 + col;
-          const bool ring = (li == 0) || (li == c.nx + 1) || (lj == 0) || (lj == c.ny + 1);
-          if ((row_in && col_in) || ring) pout[(size_t)li * S_pitch + (lj + kColOff)] = v;
+          if (store) pout[(size_t)(li0 - 1 + er) * S_pitch + (lj0 - 1 + ec + kColOff)] = v;
         };
-        if (full) {
-          constexpr int kCells = (TX + 2) * EC;
+        {
+          const int c0 = threadIdx.x % TY, r00 = threadIdx.x / TY;
+          if (full) {
 #pragma unroll
-          for (int q = 0; q < (kCells + kThreads - 1) / kThreads; ++q) {
-            const int e = threadIdx.x + q * kThreads;
-            if (e < kCells) ab_cell(e);
+            for (int q = 0; q < TX / (kThreads / TY); ++q) p_cell(r00 + q * (kThreads / TY) + 1, c0 + 1, true);
+          } else if (c0 < cy) {
+            for (int r0 = r00; r0 < cx; r0 += kThreads / TY) p_cell(r0 + 1, c0 + 1, true);
           }
-        } else {
-          for (int e = threadIdx.x; e < (cx + 2) * EC; e += kThreads) ab_cell(e);
+          // ring cells are stored to global memory only where they are ring cells of the whole block
+          if (threadIdx.x < 2 * TY) {
+            const int side = threadIdx.x / TY, cc = threadIdx.x - side * TY;
+            if (cc < cy) p_cell(side ? cx + 1 : 0, cc + 1, side ? (li0 + cx - 1 == c.nx) : (li0 == 1));
+          } else if (threadIdx.x < 2 * TY + 2 * TX) {
+            const int t = threadIdx.x - 2 * TY, side = t / TX, rr = t - side * TX;
+            if (rr < cx) p_cell(rr + 1, side ? cy + 1 : 0, side ? (lj0 + cy - 1 == c.ny) : (lj0 == 1));
+          }
         }
         __syncthreads();
         // 2. Ap = A p_new on the owned nodes of the tile
@@ -437,6 +441,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const bool full = (cx == TX) && (cy == TY);
       const int tmode = tile_mode(j);  // CTA-uniform
       const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
+      const bool edge_tile = has_nbr && (li0 == 1 || li0 + cx - 1 == c.nx || lj0 == 1 || lj0 + cy - 1 == c.ny);
       auto run_tile = [&](auto uniform) {
         constexpr bool U = decltype(uniform)::value;
         // loads and arithmetic of one node; stores and halo stores included
@@ -455,12 +460,14 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           dw = __dsub_rn(w_new, w_old);
           z = U ? div_known<DIV>(r_new, dg, rc) : div_var<DIV>(r_new, s_D[e]);
           rn = r_new;
-          if (li == 1 && c.nbr_r[kXm])
-            c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
-          if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
-          if (lj == 1 && c.nbr_r[kYm])
-            c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
-          if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+          if (edge_tile) {  // halo: our edge values become the neighbour's ring (peer stores over NVLink)
+            if (li == 1 && c.nbr_r[kXm])
+              c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
+            if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
+            if (lj == 1 && c.nbr_r[kYm])
+              c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
+            if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+          }
         };
         if (full) {
           constexpr int kPer = TX / (kThreads / TY);
