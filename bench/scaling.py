@@ -52,6 +52,7 @@ def main():
                "status": best["status_name"], "seconds": best["seconds"], "us_per_iter": us,
                "l2_error_in_D": best["l2_in_D"], "roofline_us_per_iter": 1e6 * 112.0 * nodes / world / hbm,
                "fraction_of_hbm_roofline": (112.0 * nodes / world / hbm) / (us * 1e-6),
+               "fraction_of_hbm_roofline_80B_moved": (80.0 * nodes / world / hbm) / (us * 1e-6),
                "timers_s": {k: best[k] for k in ("t_assemble", "t_gpu", "t_comm", "t_dot")}}
         if rank == 0:
             print(json.dumps(out), flush=True)
