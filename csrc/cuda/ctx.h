@@ -64,7 +64,8 @@ struct RankCtx {
   // Coefficient classes, one byte per cell, same (row, column) indexing as the fp64 arrays with row pitch
   // `pitch` bytes: bits 0-1 class of a, bits 2-3 class of b, bits 4-5 class of D; class 0 = the value of a cell
   // whose faces lie inside the ellipse (a = b = 1), 1 = outside (1/eps), 2 = anything else (read the array).
-  // All but O(M+N) cells are class 0 or 1, so the kernels stream one byte instead of three doubles.
+  // All but O(M+N) cells are class 0 or 1; the TMA kernel classifies whole tiles from these bytes once per
+  // launch and loads coefficient boxes only for tiles that are not uniformly class 0 or class 1.
   unsigned char* cls;
   // neighbour r arrays as seen from this GPU (peer mapped), with their row pitch and extents
   double* nbr_r[4];
@@ -93,6 +94,6 @@ constexpr int kTileY = 64;  // columns per stencil tile
 inline size_t arena_bytes(const LocalBlock& b) {
   return kHeaderBytes + 8 * b.elems() * sizeof(double) + ((b.elems() + 255) / 256) * 256;
 }
-constexpr int kMapsPerVariant = 16;  // tensor maps per tile height (14 used)
+constexpr int kMapsPerVariant = 16;  // tensor-map slots per tile height (12 used, see persistent_tma.cu)
 
 }  // namespace pb
