@@ -24,7 +24,7 @@ double now_s() {
 }
 
 void usage() {
-  std::cout << "usage: poisson_b200 [M N] [--gpus G] [--grid PxxPy] [--virtual] [--norm weighted|unweighted]\n"
+  std::cout << "usage: poisson_b200 [M N] [--gpus G] [--grid PxxPy|reference|auto] [--virtual] [--norm weighted|unweighted]\n"
                "                    [--delta D] [--max-iter K] [--method persistent|step_fused|step_classic]\n"
                "                    [--fast-div] [--dump FILE] [--stage 0|1|4] [--threads T] [--quiet-extras]\n";
 }
@@ -58,7 +58,7 @@ void print_extras(const pb_stats& st) {
 int main(int argc, char** argv) {
   const double t_program_start = now_s();
   int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4, threads = 1;
-  bool virt = false, extras = true;
+  bool virt = false, extras = true, ref_grid = false;
   std::string dump, method = "persistent";
   pb_solve_options opt{};
   opt.method = PB_METHOD_PERSISTENT;
@@ -82,7 +82,8 @@ int main(int argc, char** argv) {
     if (a == "--gpus") gpus = std::atoi(next().c_str());
     else if (a == "--grid") {
       const std::string g = next();
-      if (std::sscanf(g.c_str(), "%dx%d", &Px, &Py) != 2) { usage(); return 2; }
+      if (g == "reference") ref_grid = true;
+      else if (g != "auto" && std::sscanf(g.c_str(), "%dx%d", &Px, &Py) != 2) { usage(); return 2; }
     } else if (a == "--virtual") virt = true;
     else if (a == "--norm") { opt.norm = next() == "unweighted" ? PB_NORM_UNWEIGHTED : PB_NORM_WEIGHTED; norm_set = true; }
     else if (a == "--delta") opt.delta = std::atof(next().c_str());
@@ -135,7 +136,16 @@ int main(int argc, char** argv) {
     return 1;
   }
   int nranks = virt ? (Px > 0 ? Px * Py : gpus) : gpus;
-  if (Px == 0) pb_choose_proc_grid(nranks, &Px, &Py);
+  if (Px == 0) {
+    // default: slabs along x behind an NVSwitch (contiguous halo rows); --grid reference restores
+    // the reference's near-square choice (S4:82-86)
+    if (!ref_grid && nranks > 1 && (M - 1) / nranks >= 32) {
+      Px = nranks;
+      Py = 1;
+    } else {
+      pb_choose_proc_grid(nranks, &Px, &Py);
+    }
+  }
   if (Px * Py != nranks) {
     std::cerr << "error: --grid " << Px << "x" << Py << " does not match " << nranks << " ranks\n";
     return 2;

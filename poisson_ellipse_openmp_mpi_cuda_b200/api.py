@@ -5,6 +5,7 @@ Backends
 ``fused``    GPU, the product: persistent cooperative kernel, peer-memory halos, in-kernel reductions.  Uses
              every rank of the current ``torch.distributed`` group (one process per GPU), or one GPU when
              there is no group.
+``group``    GPU, same kernels, but all ``gpus`` devices driven from this one process (no launcher needed).
 ``virtual``  one GPU emulating a ``Px x Py`` process grid inside one cooperative launch (tests, what-if runs).
 ``nccl``     GPU, library-collective baseline (step kernels + NCCL send/recv + all-reduce).
 ``cpu``      whole-domain CPU solver (serial or OpenMP): the reference's stages 0/1 and our oracle.
@@ -31,7 +32,7 @@ _NORM = {"weighted": 0, "unweighted": 1}
 class PoissonSolver:
     """A solver bound to one grid size and backend; ``solve()`` may be called repeatedly."""
 
-    def __init__(self, M: int, N: int, backend: str = "auto", grid=None, threads: int = 1):
+    def __init__(self, M: int, N: int, backend: str = "auto", grid=None, threads: int = 1, gpus: int | None = None):
         if M < 2 or N < 2:
             raise ValueError("M and N must be >= 2")
         if backend == "auto":
@@ -50,6 +51,13 @@ class PoissonSolver:
 
                 self._impl = GpuSolver(M, N).finalize()
                 self.grid = (1, 1)
+        elif backend == "group":
+            from .ops.gpu import GroupSolver
+            from .parallel.decomp import parse_grid as _pg
+
+            n = torch.cuda.device_count() if gpus is None else int(gpus)
+            self.grid = _pg("auto" if grid is None else grid, n, M)
+            self._impl = GroupSolver(M, N, self.grid[0], self.grid[1])
         elif backend == "virtual":
             from .ops.gpu import GpuSolver
 
@@ -76,7 +84,7 @@ class PoissonSolver:
         """Run one solve; returns the report (iterations, status, norms, errors, timers)."""
         mi = -1 if max_iter is None else int(max_iter)
         t0 = time.perf_counter()
-        if self.backend in ("fused", "virtual"):
+        if self.backend in ("fused", "virtual", "group"):
             res = self._impl.solve(method=method, norm=norm, delta=delta, max_iter=mi, div=div, **kw)
         elif self.backend in ("nccl", "cpu_dist"):
             res = self._impl.solve(norm=norm, delta=delta, max_iter=mi, div=div)
@@ -103,7 +111,7 @@ class PoissonSolver:
             if self._w is None:
                 raise RuntimeError("solve() first")
             return self._w
-        if self.backend == "virtual" or (self.backend == "fused" and self.world == 1):
+        if self.backend in ("virtual", "group") or (self.backend == "fused" and self.world == 1):
             return self._impl.solution_host()
         import torch.distributed as dist
 
@@ -131,16 +139,18 @@ _CACHE: dict = {}
 
 def solve(M: int, N: int, backend: str = "auto", grid=None, norm: str = "weighted", delta: float = 1e-6,
           max_iter: int | None = None, threads: int = 1, dump: str | None = None, return_solution: bool = False,
-          **kw):
+          gpus: int | None = None, **kw):
     """Solve the fictitious-domain Poisson problem on an ``M x N`` grid.
 
     Returns the report dict, or ``(report, w)`` with ``return_solution=True``.  Solvers are cached per
     ``(M, N, backend, grid, threads)`` so repeated calls reuse device memory and peer mappings.
     """
-    key = (M, N, backend, str(grid), threads, world_info())
+    if gpus is not None and gpus > 1 and backend in ("auto", "fused") and world_info()[1] == 1:
+        backend = "group"  # several GPUs, one process
+    key = (M, N, backend, str(grid), threads, gpus, world_info())
     solver = _CACHE.get(key)
     if solver is None:
-        solver = _CACHE[key] = PoissonSolver(M, N, backend, grid, threads)
+        solver = _CACHE[key] = PoissonSolver(M, N, backend, grid, threads, gpus)
     res = solver.solve(norm=norm, delta=delta, max_iter=max_iter, **kw)
     w = None
     if dump or return_solution:

@@ -200,3 +200,51 @@ class GpuSolver:
         _native.check(self.lib.pb_step_read_control(self._h, local_idx, C.byref(it), C.byref(stt), C.byref(dn),
                                                     _stream_ptr(None)), "pb_step_read_control")
         return {"iters": it.value, "status": stt.value, "diff_norm": dn.value}
+
+
+class GroupSolver:
+    """Several GPUs driven from this one process (peer access inside the process, one persistent kernel per device):
+    the multi-GPU form that needs no launcher.  ``devices`` defaults to ``0..G-1``."""
+
+    def __init__(self, M: int, N: int, Px: int, Py: int, devices=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("GroupSolver needs CUDA devices")
+        self.lib = _native.lib()
+        self.M, self.N, self.Px, self.Py = M, N, Px, Py
+        devs = list(range(Px * Py)) if devices is None else list(devices)
+        if len(devs) != Px * Py:
+            raise ValueError("one device per rank is required")
+        torch.cuda.init()
+        arr = (C.c_int * len(devs))(*devs)
+        self._h = self.lib.pb_group_create(M, N, Px, Py, arr, len(devs))
+        if not self._h:
+            raise RuntimeError(f"pb_group_create failed: {_native.last_error()}")
+
+    def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
+              div: str = "markstein", watchdog_s: float = 0.0, tile_rows: int = 0, l2_hints: bool = False,
+              full_coefficients: bool = False, **_ignored) -> dict:
+        opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, DIVS[div], 0, 1, tile_rows, watchdog_s,
+                                   int(l2_hints), int(full_coefficients))
+        st = _native.Stats()
+        _native.check(self.lib.pb_group_solve(self._h, C.byref(opt), C.byref(st)), "pb_group_solve")
+        out = st.as_dict()
+        out["status_name"] = STATUS.get(st.status, "?")
+        if st.status in (4, 5):
+            raise RuntimeError(f"device-side {STATUS[st.status]}: the solve was abandoned")
+        return out
+
+    def solution_host(self) -> torch.Tensor:
+        full = torch.zeros((self.M + 1, self.N + 1), dtype=torch.float64)
+        _native.check(self.lib.pb_group_copy_solution(self._h, full.data_ptr()), "pb_group_copy_solution")
+        return full
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.pb_group_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

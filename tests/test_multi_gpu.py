@@ -94,3 +94,18 @@ def test_in_process_group_cli(ngpu):
     assert f"MPI + CUDA 2D run with {ngpu} processes; M=400, N=600" in out.stdout
     assert "Converged after 546 iterations (||w(k+1)-w(k)|| < 1e-06)." in out.stdout
     assert "M=400, N=600 | Iter=546 | Total Time=" in out.stdout
+
+
+@pytest.mark.parametrize("ngpu", [2, 8])
+def test_python_group_backend(native, ngpu):
+    """solve(..., gpus=G): several GPUs from one process, no launcher."""
+    import poisson_b200 as pb
+
+    if _ngpu() < ngpu:
+        pytest.skip(f"needs {ngpu} GPUs")
+    res, w = pb.solve(400, 600, gpus=ngpu, return_solution=True)
+    assert res["iters"] == 546 and res["status_name"] == "converged"
+    assert res["l2_in_D"] == pytest.approx(ERRORS[(400, 600)][0], rel=2e-6)
+    ref, _ = _reference_field(native, 400, 600)
+    assert torch.allclose(w, ref, rtol=0, atol=1e-12)
+    pb.clear_cache()
