@@ -107,5 +107,5 @@ def test_python_group_backend(native, ngpu):
     assert res["iters"] == 546 and res["status_name"] == "converged"
     assert res["l2_in_D"] == pytest.approx(ERRORS[(400, 600)][0], rel=2e-6)
     ref, _ = _reference_field(native, 400, 600)
-    assert torch.allclose(w, ref, rtol=0, atol=1e-12)
+    assert torch.allclose(w, ref, rtol=0, atol=1e-11)  # 546 iterations, different summation order
     pb.clear_cache()
