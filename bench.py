@@ -133,8 +133,9 @@ def run_ours(a) -> dict:
         launches += res.get("launches", 0)
     sync()
     t_wall = time.perf_counter() - t_wall0
-    # ---- end-to-end through the public API ----
+    # ---- end-to-end through the public API (first call builds and caches the solver: untimed warm-up) ----
     e2e_s = []
+    pb.solve(M, N, backend="fused", grid=a.grid, **kw)
     for _ in range(a.steps):
         flush.fill_(1)
         sync()
