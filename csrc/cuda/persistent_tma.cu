@@ -346,8 +346,20 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         {
           const int c0 = threadIdx.x % TY, r00 = threadIdx.x / TY;
           if (full) {
+            // same as p_cell(r00 + 8 q + 1, c0 + 1, true), with the index arithmetic hoisted out of the unrolled body
+            constexpr int kRows = kThreads / TY;
+            const double* sr = s_r + (r00 + 1) * EC + c0 + 2;
+            double* sp = s_p + (r00 + 1) * EC + c0 + 2;
+            const double* sd = s_D + (r00 + 1) * EC + c0 + 2;
+            double* po = pout + (size_t)(li0 + r00) * S_pitch + (lj0 + c0 + kColOff);
+            const size_t gstep = (size_t)kRows * S_pitch;
 #pragma unroll
-            for (int q = 0; q < TX / (kThreads / TY); ++q) p_cell(r00 + q * (kThreads / TY) + 1, c0 + 1, true);
+            for (int q = 0; q < TX / kRows; ++q) {
+              const double z = U ? div_known<DIV>(sr[q * kRows * EC], dg, rc) : div_var<DIV>(sr[q * kRows * EC], sd[q * kRows * EC]);
+              const double v = fma(beta, sp[q * kRows * EC], z);
+              sp[q * kRows * EC] = v;
+              po[q * gstep] = v;
+            }
           } else if (c0 < cy) {
             for (int r0 = r00; r0 < cx; r0 += kThreads / TY) p_cell(r0 + 1, c0 + 1, true);
           }
@@ -378,10 +390,29 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           return v;
         };
         if (full) {
-          constexpr int kPer = TX / (kThreads / TY);  // nodes per thread
+          // same as ab_node(r00 + 8 q + 1), index arithmetic hoisted
+          constexpr int kRows = kThreads / TY, kPer = TX / kRows;  // nodes per thread
+          const int r00 = threadIdx.x / TY;
+          const double* sp = s_p + (r00 + 1) * EC + col + 1;
+          const double* sa = s_a + r00 * TY + (col - 1);
+          const double* sb2 = s_b + r00 * BC + (col - 1);
+          double* ap = c.Ap + (size_t)(li0 + r00) * S_pitch + (lj0 - 1 + col + kColOff);
+          const size_t gstep = (size_t)kRows * S_pitch;
           double v[kPer], pc[kPer];
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) v[q] = ab_node(threadIdx.x / TY + 1 + q * (kThreads / TY), pc[q]);
+          for (int q = 0; q < kPer; ++q) {
+            const double* s = sp + q * kRows * EC;
+            pc[q] = s[0];
+            double a_c, a_ip, b_c, b_jp;
+            if constexpr (U) {
+              a_c = a_ip = b_c = b_jp = cf;
+            } else {
+              a_c = sa[q * kRows * TY], a_ip = sa[q * kRows * TY + TY];
+              b_c = sb2[q * kRows * BC], b_jp = sb2[q * kRows * BC + 1];
+            }
+            v[q] = stencil_value<DIV>(K, pc[q], s[-EC], s[EC], s[-1], s[1], a_c, a_ip, b_c, b_jp);
+            ap[q * gstep] = v[q];
+          }
 #pragma unroll
           for (int q = 0; q < kPer; ++q) acc_ab = fma(v[q], pc[q], acc_ab);  // same order as the generic loop
         } else if (col <= cy) {
@@ -469,7 +500,34 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
             if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
           }
         };
-        if (full) {
+        if (full && !edge_tile) {
+          // same as c_node(r00 + 8 q) without the halo stores, index arithmetic hoisted
+          constexpr int kRows = kThreads / TY, kPer = TX / kRows;
+          const int r00 = threadIdx.x / TY, e0 = r00 * TY + col;
+          double* pw = c.w + (size_t)(li0 + r00) * S_pitch + (lj0 + col + kColOff);
+          double* pr = c.r + (size_t)(li0 + r00) * S_pitch + (lj0 + col + kColOff);
+          const size_t gstep = (size_t)kRows * S_pitch;
+          double dw[kPer], z[kPer], rn[kPer];
+#pragma unroll
+          for (int q = 0; q < kPer; ++q) {
+            const int e = e0 + q * kRows * TY;
+            const double w_old = s_w[e];
+            const double w_new = fma(alpha, s_p[e], w_old);
+            rn[q] = fma(-alpha, s_Ap[e], s_r[e]);
+            if (l2_hints)
+              __stcs(pw + q * gstep, w_new);
+            else
+              pw[q * gstep] = w_new;
+            pr[q * gstep] = rn[q];
+            dw[q] = __dsub_rn(w_new, w_old);
+            z[q] = U ? div_known<DIV>(rn[q], dg, rc) : div_var<DIV>(rn[q], s_D[e]);
+          }
+#pragma unroll
+          for (int q = 0; q < kPer; ++q) {
+            acc_d = fma(dw[q], dw[q], acc_d);
+            acc_zr = fma(z[q], rn[q], acc_zr);
+          }
+        } else if (full) {
           constexpr int kPer = TX / (kThreads / TY);
           double dw[kPer], z[kPer], rn[kPer];
 #pragma unroll
