@@ -39,7 +39,7 @@ struct Control {
   int iter;                  // index of the current / final iteration
   int status;                // PB_STATUS_*
   unsigned int red_seq;      // sequence number of the last cross-rank reduction (persists across solves)
-  unsigned int arrive_base;  // value of the arrival counter at the start of the next reduction
+  unsigned int halo_seq;     // sequence number of the last halo round (persists across solves, like red_seq)
   int cur;                   // which p buffer holds the current direction
   int pad0;
   // options
@@ -81,6 +81,14 @@ struct RankCtx {
   // counter that our stores into its ring must bump (its opposite direction)
   unsigned long long* halo_cnt;
   unsigned long long* nbr_halo_cnt[4];
+  // Fence-free halo lines (TMA kernel): per direction and parity a line of (payload32 | seq32) word pairs, one pair
+  // per edge node, written by the neighbour and unpacked into our r ring by the warp that issues the tile's loads.
+  // halo_ll = [4 directions][2 parities][ll_cap][2] u64 of this rank; nbr_ll[d] = the neighbour's line block for
+  // ITS direction d^1 (what our edge d feeds), nbr_ll_cap[d] its capacity.
+  unsigned long long* halo_ll;
+  int ll_cap;
+  unsigned long long* nbr_ll[4];
+  int nbr_ll_cap[4];
   const void* tmaps;  // CUtensorMap[2][12] in device memory (TMA persistent kernel), see persistent_tma.cu
   int sys_scope;  // 1: some peer lives on another device, fences must be system-wide
   // tiling of the block for the stencil phase
@@ -91,9 +99,11 @@ constexpr int kTileX = 32;  // rows per stencil tile
 constexpr int kTileY = 64;  // columns per stencil tile
 
 // 8 fp64 arrays + one byte per cell of coefficient classes (see RankCtx::cls)
-inline size_t arena_bytes(const LocalBlock& b) {
-  return kHeaderBytes + 8 * b.elems() * sizeof(double) + ((b.elems() + 255) / 256) * 256;
-}
+inline size_t cls_bytes(const LocalBlock& b) { return ((b.elems() + 255) / 256) * 256; }
+inline int ll_capacity(const LocalBlock& b) { return (b.nx > b.ny ? b.nx : b.ny) + 2; }
+inline size_t halo_ll_offset(const LocalBlock& b) { return kHeaderBytes + 8 * b.elems() * sizeof(double) + cls_bytes(b); }
+inline size_t halo_ll_bytes(const LocalBlock& b) { return (size_t)4 * 2 * ll_capacity(b) * 2 * sizeof(unsigned long long); }
+inline size_t arena_bytes(const LocalBlock& b) { return halo_ll_offset(b) + halo_ll_bytes(b); }
 constexpr int kMapsPerVariant = 16;  // tensor-map slots per tile height (12 used, see persistent_tma.cu)
 
 }  // namespace pb

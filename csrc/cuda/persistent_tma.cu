@@ -68,6 +68,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   __shared__ double s_red[80];
   __shared__ __align__(8) uint64_t s_bar[S];
   __shared__ unsigned char s_tclass[kMaxTileClass];
+  __shared__ int s_filled[S];  // per stage: ring cells were unpacked for the tile in flight (thread 0 only)
   extern __shared__ __align__(128) unsigned char s_dyn[];
 
   const int vrank = blockIdx.x / ctas_per_rank;
@@ -79,7 +80,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     for (int i = threadIdx.x; i < (int)(sizeof(RankCtx) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) mbar_init(&s_bar[s], 1);
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&s_bar[s], 1);
+      s_filled[s] = 0;
+    }
     mbar_fence_init();
   }
   __syncthreads();
@@ -93,9 +97,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const int ntiles = tiles_x * tiles_y;
   const int nmine = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
   // Tile order: row-major, except that the last tile row is visited right after the first one.  The tiles
-  // that store halo rows into the x-neighbours (phase C) and the tiles that need the neighbours' rows
-  // (phase AB) then come first on both sides, so the system-scope release of the stores and the NVLink
-  // latency hide behind the remaining tiles instead of sitting in front of a reduction.  (Enumerating the
+  // that store halo rows for the x-neighbours (phase C) and the tiles that need the neighbours' rows
+  // (phase AB) then come first on both sides, so the NVLink latency of the halo records hides behind the
+  // remaining tiles instead of sitting in front of a reduction.  (Enumerating the
   // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
   const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
@@ -129,18 +133,6 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     li0 = 1 + tx * TX;
     lj0 = 1 + ty * TY;
   };
-  // index of my last tile that touches an edge shared with a neighbour (-1: none)
-  int last_halo_j = -1;
-  if (has_nbr) {
-    for (int j = 0; j < nmine; ++j) {
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
-      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
-      if ((li0 == 1 && c.nbr_r[kXm]) || (li0 + cx - 1 == c.nx && c.nbr_r[kXp]) || (lj0 == 1 && c.nbr_r[kYm]) ||
-          (lj0 + cy - 1 == c.ny && c.nbr_r[kYp]))
-        last_halo_j = j;
-    }
-  }
   // Tile classes: 0 = every cell of the tile and its ring is "inside" (a = b = 1, D = diag_in), 1 = all
   // "outside" (1/eps, diag_out), 2 = mixed (full coefficient boxes).  One pass over the class bytes per launch.
   if constexpr (CC) {
@@ -163,50 +155,64 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   }
   auto tile_mode = [&](int j) -> int { return (CC && j < kMaxTileClass) ? (int)s_tclass[j] : 2; };
 
-  // Halo completion counters (see ctx.h): value at launch, and by how much one phase C of the neighbour
-  // raises ours (= the number of its tiles along the shared edge).
-  unsigned long long halo_base[4];
-  int edge_tiles[4];
-#pragma unroll
-  for (int d = 0; d < 4; ++d) {
-    halo_base[d] = ld_relaxed_sys_u64(c.halo_cnt + d);
-    edge_tiles[d] = c.nbr_r[d] ? (d < 2 ? (c.nbr_ny[d] + TY - 1) / TY : (c.nbr_nx[d] + TX - 1) / TX) : 0;
-  }
-  // thread 0: wait until the ring cells of the tile at (li0, lj0) hold the neighbours' r of round `rounds`
-  auto wait_halo = [&](int li0, int lj0, long long rounds) -> bool {
+  // Halo rows travel as LL records (payload32 | sequence32 word pairs, see ctx.h): the producer needs no fence and
+  // no counter, the consumer recognises complete values by their sequence number.  Round k of this launch
+  // carries sequence hseq + k; the number persists across launches like red_seq.
+  const unsigned int hseq = ctl->halo_seq;
+  // warp 0: copy the neighbours' r values of round `rounds` for the ring cells of the tile at (li0, lj0) from the
+  // halo lines into our r ring; returns whether the tile touches a shared edge at all
+  auto unpack_halo = [&](int li0, int lj0, long long rounds) -> bool {
     const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
     const bool touch[4] = {li0 == 1, li0 + cx - 1 == c.nx, lj0 == 1, lj0 + cy - 1 == c.ny};
-    bool waited = false;
+    const unsigned int want = hseq + (unsigned int)rounds;
+    const unsigned long long limit = ctl->watchdog_ns ? ctl->watchdog_ns : kDefaultWatchdogNs;
+    const int lane = threadIdx.x & 31;
+    bool any = false;
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
       if (!touch[d] || !c.nbr_r[d]) continue;
-      waited = true;
-      const unsigned long long want = halo_base[d] + (unsigned long long)rounds * (unsigned long long)edge_tiles[d];
-      unsigned long long t0 = 0;
-      unsigned int spins = 0;
-      while (ld_acquire_sys_u64(c.halo_cnt + d) < want) {
-        if ((++spins & 0xffu) == 0u) {
-          const unsigned long long now = globaltimer_ns();
-          if (t0 == 0) t0 = now;
-          if (now - t0 > (ctl->watchdog_ns ? ctl->watchdog_ns : kDefaultWatchdogNs)) {
-            ctl->red[2] = 1.0;  // sticky marker (zeroed by the host before the launch): halo wait timed out
-            break;
+      any = true;
+      const unsigned long long* line = c.halo_ll + ((size_t)d * 2 + (want & 1u)) * (size_t)c.ll_cap * 2;
+      const int t0 = d < 2 ? lj0 - 1 : li0 - 1, n = d < 2 ? cy : cx;
+      for (int i = lane; i < n; i += 32) {
+        const unsigned long long* src = line + (size_t)(t0 + i) * 2;
+        unsigned long long w0, w1, tstart = 0;
+        unsigned int spins = 0;
+        while (true) {
+          w0 = ld_relaxed_sys_u64(src), w1 = ld_relaxed_sys_u64(src + 1);
+          if ((unsigned int)(w0 >> 32) == want && (unsigned int)(w1 >> 32) == want) break;
+          if ((++spins & 0xffu) == 0u) {
+            const unsigned long long now = globaltimer_ns();
+            if (tstart == 0) tstart = now;
+            if (now - tstart > limit) {
+              ctl->red[2] = 1.0;  // sticky marker (zeroed by the host before the launch): halo wait timed out
+              break;
+            }
           }
         }
+        const double v = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+        const int li = d == kXm ? 0 : (d == kXp ? c.nx + 1 : t0 + i + 1);
+        const int lj = d == kYm ? 0 : (d == kYp ? c.ny + 1 : t0 + i + 1);
+        c.r[(size_t)li * S_pitch + (lj + kColOff)] = v;
       }
     }
-    return waited;
+    __syncwarp();
+    return any;
   };
   // Phase-AB loads of tile j into stage `st`.  part 1 = everything that does not depend on the other CTAs'
   // phase C (p and, for mixed tiles, D, a, b; arms the barrier with the full byte count), part 2 = the r box.
   auto issue_ab_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2, long long rounds) {
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {
       int li0, lj0;
       tile_origin(j, li0, lj0);
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
       const int x = kColOff + lj0 - 2, y = li0 - 1;  // even column: 16-byte aligned box start
-      if (part1) {
+      // A tile on a shared edge gets its ring cells filled from the halo lines by the whole warp.  This depends
+      // only on the neighbour GPU, so it belongs to part 1 and its latency hides in the reduction that follows.
+      const bool filled = part1 && has_nbr && rounds > 0 && unpack_halo(li0, lj0, rounds);
+      if (part1 && threadIdx.x == 0) {
+        if (filled) s_filled[st] = 1;
         const bool coef = tile_mode(j) == 2;
         fence_proxy_async_smem();
         mbar_arrive_expect_tx(bar, Cfg::kTxABCore + (coef ? Cfg::kTxABCoef : 0u));
@@ -218,9 +224,14 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         }
       }
       if (part2) {
-        // only a tile on a shared edge reads cells another GPU wrote since the phase-start fence
-        if (has_nbr && wait_halo(li0, lj0, rounds)) fence_proxy_async();  // acquired generic-proxy stores -> TMA read
-        tma_load_2d_hint(sb + Cfg::kOffR, maps + kMapRExt, x, y, bar, pol_keep);
+        if (threadIdx.x == 0) {
+          // the elected lane orders the ring cells written above (generic proxy) before the TMA read of the box
+          if (s_filled[st]) {
+            fence_proxy_async();
+            s_filled[st] = 0;
+          }
+          tma_load_2d_hint(sb + Cfg::kOffR, maps + kMapRExt, x, y, bar, pol_keep);
+        }
       }
     }
   };
@@ -455,7 +466,6 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     alpha = zr_old / denom;
     // ======================= phase C =======================
     double acc_d = 0.0, acc_zr = 0.0;
-    int pushed[4] = {0, 0, 0, 0};  // tiles of this CTA whose edge values went into each neighbour's ring
     for (int j = 0; j < nmine && tma_ok; ++j) {
       if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
       unsigned char* sb = wait_stage();
@@ -491,13 +501,20 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           dw = __dsub_rn(w_new, w_old);
           z = U ? div_known<DIV>(r_new, dg, rc) : div_var<DIV>(r_new, s_D[e]);
           rn = r_new;
-          if (edge_tile) {  // halo: our edge values become the neighbour's ring (peer stores over NVLink)
-            if (li == 1 && c.nbr_r[kXm])
-              c.nbr_r[kXm][(size_t)(c.nbr_nx[kXm] + 1) * c.nbr_pitch[kXm] + (lj + kColOff)] = r_new;
-            if (li == c.nx && c.nbr_r[kXp]) c.nbr_r[kXp][(size_t)(lj + kColOff)] = r_new;
-            if (lj == 1 && c.nbr_r[kYm])
-              c.nbr_r[kYm][(size_t)li * c.nbr_pitch[kYm] + (c.nbr_ny[kYm] + 1 + kColOff)] = r_new;
-            if (lj == c.ny && c.nbr_r[kYp]) c.nbr_r[kYp][(size_t)li * c.nbr_pitch[kYp] + kColOff] = r_new;
+          if (edge_tile) {  // halo: our edge values go into the neighbour's halo line (peer stores over NVLink)
+            const unsigned int hs = hseq + (unsigned int)k;
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(r_new);
+            const unsigned long long w0 = (bits & 0xffffffffull) | ((unsigned long long)hs << 32);
+            const unsigned long long w1 = (bits >> 32) | ((unsigned long long)hs << 32);
+            auto push = [&](int d, int t) {
+              unsigned long long* dst = c.nbr_ll[d] + ((size_t)(hs & 1u) * (size_t)c.nbr_ll_cap[d] + (size_t)t) * 2;
+              st_relaxed_sys_u64(dst, w0);
+              st_relaxed_sys_u64(dst + 1, w1);
+            };
+            if (li == 1 && c.nbr_r[kXm]) push(kXm, lj - 1);
+            if (li == c.nx && c.nbr_r[kXp]) push(kXp, lj - 1);
+            if (lj == 1 && c.nbr_r[kYm]) push(kYm, li - 1);
+            if (lj == c.ny && c.nbr_r[kYp]) push(kYp, li - 1);
           }
         };
         if (full && !edge_tile) {
@@ -550,21 +567,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         run_tile(std::true_type{});
       else
         run_tile(std::false_type{});
-      if (has_nbr && j <= last_halo_j) {
-        pushed[kXm] += (li0 == 1), pushed[kXp] += (li0 + cx - 1 == c.nx);
-        pushed[kYm] += (lj0 == 1), pushed[kYp] += (lj0 + cy - 1 == c.ny);
-      }
-      __syncthreads();  // stage free; all halo stores of this tile are issued
-      // Release the halo stores of this CTA's edge tiles system-wide and count them in at the neighbour --
-      // one tile after the last edge tile (or at the end of the phase), when the stores have long been
-      // acknowledged and the fence costs little; the whole CTA would otherwise wait for it at the next barrier.
-      if (has_nbr && last_halo_j >= 0 && (j == last_halo_j + 1 || (j == nmine - 1 && last_halo_j == nmine - 1)) &&
-          threadIdx.x == 32) {
-        fence_acq_rel_sys();
-#pragma unroll
-        for (int d = 0; d < 4; ++d)
-          if (pushed[d] && c.nbr_r[d]) red_add_relaxed_sys_u64(c.nbr_halo_cnt[d], (unsigned long long)pushed[d]);
-      }
+      __syncthreads();  // stage free
       ++n_consumed;
     }
     if (!tma_ok) break;
@@ -619,6 +622,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     ctl->zr_old = zr_old;
     ctl->cur = cur;
     ctl->red_seq = seq;
+    ctl->halo_seq = hseq + (unsigned int)k + 1u;
     ctl->t_ab = t_ab;
     ctl->t_c = t_c;
     ctl->t_red1 = t_r1;

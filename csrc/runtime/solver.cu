@@ -117,11 +117,16 @@ void Solver::finalize() {
         c.nbr_r[d] = reinterpret_cast<double*>(static_cast<char*>(peer_base_[b.nbr[d]]) + kHeaderBytes);
         c.nbr_pitch[d] = nb.pitch, c.nbr_nx[d] = nb.nx, c.nbr_ny[d] = nb.ny;
         c.nbr_halo_cnt[d] = reinterpret_cast<unsigned long long*>(static_cast<char*>(peer_base_[b.nbr[d]]) + kHaloCntOffset) + (d ^ 1);
+        c.nbr_ll_cap[d] = ll_capacity(nb);
+        c.nbr_ll[d] = reinterpret_cast<unsigned long long*>(static_cast<char*>(peer_base_[b.nbr[d]]) + halo_ll_offset(nb)) +
+                      (size_t)(d ^ 1) * 2 * c.nbr_ll_cap[d] * 2;
       }
     }
     c.partials = reinterpret_cast<double*>(arenas_[l] + kPartialsOffset);
     c.arrive = reinterpret_cast<unsigned int*>(arenas_[l] + kArriveOffset);
     c.halo_cnt = reinterpret_cast<unsigned long long*>(arenas_[l] + kHaloCntOffset);
+    c.halo_ll = reinterpret_cast<unsigned long long*>(arenas_[l] + halo_ll_offset(b));
+    c.ll_cap = ll_capacity(b);
     c.slots = reinterpret_cast<unsigned long long*>(arenas_[l] + kSlotsOffset);
     for (int rk = 0; rk < nranks(); ++rk)
       if (peer_base_[rk])
