@@ -4,7 +4,9 @@
 // S4:995-999; delta = 1e-6 and max_iter = (M-1)(N-1), S4:1005-1006) and prints the stage-4 report verbatim
 // (S4:1001-1002, S4:900-902, S4:969-978, S4:1027-1033), followed by the lines the reference lacks (error
 // against the analytic solution, device time per iteration).  `--stage 0|1` selects the CPU programs'
-// behaviour and formats (S0:176-196, S1:204-229).
+// behaviour and formats (S0:176-196, S1:204-229): stage 0 without M N sweeps the grids the reference hard-codes
+// (10^2, 20^2, 40^2, S0:177; `--grids` overrides), stage 1 prints the reference's banner block and one line per
+// entry of `--threads a,b,c` (S1:208-226).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -26,7 +28,8 @@ double now_s() {
 void usage() {
   std::cout << "usage: poisson_b200 [M N] [--gpus G] [--grid PxxPy|reference|auto] [--virtual] [--norm weighted|unweighted]\n"
                "                    [--delta D] [--max-iter K] [--method persistent|step_fused|step_classic]\n"
-               "                    [--fast-div] [--dump FILE] [--stage 0|1|4] [--threads T] [--quiet-extras]\n";
+               "                    [--fast-div] [--dump FILE] [--stage 0|1|4] [--threads T[,T...]] [--grids MxN[,MxN...]]\n"
+               "                    [--quiet-extras]\n";
 }
 
 void dump_solution(const std::string& path, const std::vector<double>& w, int M, int N) {
@@ -46,6 +49,19 @@ void dump_solution(const std::string& path, const std::vector<double>& w, int M,
   }
 }
 
+// "4,8,16" -> {4,8,16}; "10x10,20x20" -> {10,10,20,20}
+std::vector<int> parse_int_list(const std::string& text) {
+  std::vector<int> out;
+  size_t pos = 0;
+  while (pos < text.size()) {
+    size_t end = text.find_first_of(",x", pos);
+    if (end == std::string::npos) end = text.size();
+    out.push_back(std::atoi(text.substr(pos, end - pos).c_str()));
+    pos = end + 1;
+  }
+  return out;
+}
+
 void print_extras(const pb_stats& st) {
   std::printf("   L2 error vs analytic (in D)  ~ %.9e\n", st.l2_in_D);
   std::printf("   L2 error vs analytic (all)   ~ %.9e\n", st.l2_all);
@@ -57,7 +73,8 @@ void print_extras(const pb_stats& st) {
 
 int main(int argc, char** argv) {
   const double t_program_start = now_s();
-  int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4, threads = 1;
+  int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4;
+  std::vector<int> thread_list{1}, grid_list;
   bool virt = false, extras = true, ref_grid = false;
   std::string dump, method = "persistent";
   pb_solve_options opt{};
@@ -92,7 +109,8 @@ int main(int argc, char** argv) {
     else if (a == "--fast-div") opt.exact_div = 0;
     else if (a == "--dump") dump = next();
     else if (a == "--stage") stage = std::atoi(next().c_str());
-    else if (a == "--threads") threads = std::atoi(next().c_str());
+    else if (a == "--threads") thread_list = parse_int_list(next());
+    else if (a == "--grids") grid_list = parse_int_list(next());
     else if (a == "--quiet-extras") extras = false;
     else if (a == "-h" || a == "--help") { usage(); return 0; }
     else pos.push_back(a);
@@ -107,25 +125,40 @@ int main(int argc, char** argv) {
   // ---- CPU stages ----
   if (stage == 0 || stage == 1) {
     if (!norm_set) opt.norm = stage == 0 ? PB_NORM_UNWEIGHTED : PB_NORM_WEIGHTED;
-    std::vector<double> w((size_t)(M + 1) * (N + 1));
-    pb_stats st{};
-    if (pb_cpu_solve(M, N, opt.norm, opt.delta, opt.max_iter, stage == 0 ? 1 : threads, 1, w.data(), &st) != 0) {
-      std::cerr << "error: " << pb_last_error() << "\n";
-      return 1;
+    if (thread_list.empty() || grid_list.size() % 2 != 0) { usage(); return 2; }
+    if (grid_list.empty()) {
+      if (pos.size() >= 2 || stage == 1) grid_list = {M, N};
+      else grid_list = {10, 10, 20, 20, 40, 40};  // the reference's stage-0 program takes no arguments (S0:177)
     }
-    if (st.status == PB_STATUS_CONVERGED) {
-      if (stage == 0) std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < δ)." << std::endl;
-      else std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < " << opt.delta << ").\n";
+    for (size_t gi = 0; gi + 1 < grid_list.size(); gi += 2) {
+      M = grid_list[gi], N = grid_list[gi + 1];
+      if (stage == 1) {
+        std::cout << "--- (Variant 9: Ellipse x^2 + 4y^2 < 1, OpenMP Test) ---\n";
+        std::cout << "Grid: M=" << M << ", N=" << N << "\n";
+        std::cout << "--------------------------------------------------------\n";
+      }
+      std::vector<double> w((size_t)(M + 1) * (N + 1));
+      pb_stats st{};
+      for (int threads : (stage == 0 ? std::vector<int>{1} : thread_list)) {
+        if (pb_cpu_solve(M, N, opt.norm, opt.delta, opt.max_iter, threads, 1, w.data(), &st) != 0) {
+          std::cerr << "error: " << pb_last_error() << "\n";
+          return 1;
+        }
+        // both CPU programs print the literal symbol, not the value of delta (S0:157-158, S1:192)
+        if (st.status == PB_STATUS_CONVERGED)
+          std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < δ)." << std::endl;
+        if (stage == 0)
+          std::cout << "M=" << M << ", N=" << N << " | Iter=" << st.iters << " | Time=" << std::fixed << std::setprecision(4)
+                    << st.seconds << " s\n";
+        else
+          std::cout << "Threads = " << std::setw(2) << threads << " | Time = " << std::fixed << std::setprecision(3)
+                    << st.seconds << " s\n";
+      }
+      if (stage == 1) std::cout << "--------------------------------------------------------\n";
+      std::cout.flush();
+      if (extras) print_extras(st);
+      if (!dump.empty()) dump_solution(dump, w, M, N);
     }
-    if (stage == 0)
-      std::cout << "M=" << M << ", N=" << N << " | Iter=" << st.iters << " | Time=" << std::fixed << std::setprecision(4)
-                << st.seconds << " s\n";
-    else
-      std::cout << "Threads = " << std::setw(2) << threads << " | Time = " << std::fixed << std::setprecision(3)
-                << st.seconds << " s\n";
-    std::cout.flush();
-    if (extras) print_extras(st);
-    if (!dump.empty()) dump_solution(dump, w, M, N);
     return 0;
   }
 

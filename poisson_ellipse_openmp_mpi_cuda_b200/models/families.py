@@ -22,7 +22,40 @@ FAMILIES = {
 }
 
 
-def run_family(name: str, M: int, N: int, threads: int = 1, grid=None, delta: float = 1e-6, **kw):
+# what each argument-less reference program runs (S0:177, S0v2:188, S0v3:186; S1v1:204-215, S1v2:204-214, S1:204-214)
+REFERENCE_PROGRAMS = {
+    "stage0": {"grids": [(10, 10), (20, 20), (40, 40)]},
+    "stage0-v2": {"grids": [(400, 600)]},
+    "stage0-v3": {"grids": [(800, 1200)]},
+    "stage1-v1": {"grid": (40, 40), "threads": [1, 4, 16]},
+    "stage1-v2": {"grid": (400, 600), "threads": [2, 4, 8, 16]},
+    "stage1": {"grid": (800, 1200), "threads": [4, 8, 16, 32]},
+}
+
+
+def run_program(name: str, grids=None, grid=None, threads=None, **kw):
+    """Run a CPU reference program the way its argument-less ``main`` does and return ``(results, stdout text)``.
+
+    Stage 0 sweeps a list of grids (S0:176-196); stage 1 sweeps thread counts on one grid between a banner and a
+    closing rule (S1:204-229).  ``grids`` / ``grid`` / ``threads`` override the hard-coded lists.
+    """
+    spec = REFERENCE_PROGRAMS[name]
+    if name.startswith("stage0"):
+        out, texts = [], []
+        for M, N in (grids or spec["grids"]):
+            res, text = run_family("stage0", M, N, extras=False, **kw)
+            out.append(res)
+            texts.append(text)
+        return out, "\n".join(texts)
+    M, N = grid or spec["grid"]
+    entries = []
+    for t in (threads or spec["threads"]):
+        res, _ = run_family("stage1", M, N, threads=t, **kw)
+        entries.append((t, res, res["seconds"]))
+    return [e[1] for e in entries], report.stage1_program(M, N, entries)
+
+
+def run_family(name: str, M: int, N: int, threads: int = 1, grid=None, delta: float = 1e-6, extras: bool = True, **kw):
     backend, norm, _ = FAMILIES[name]
     rank, world = world_info()
     t_prog = time.perf_counter()
@@ -32,7 +65,7 @@ def run_family(name: str, M: int, N: int, threads: int = 1, grid=None, delta: fl
     res = solver.solve(norm=norm, delta=delta, **extra, **kw)
     t_after = time.perf_counter()
     if name == "stage0":
-        text = report.stage0_report(M, N, res, res["seconds"])
+        text = report.stage0_report(M, N, res, res["seconds"], extras=extras)
     elif name == "stage1":
         text = report.stage1_report(M, N, threads, res, delta, res["seconds"])
     elif name in ("stage2", "stage3"):

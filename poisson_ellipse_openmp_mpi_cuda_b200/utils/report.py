@@ -74,9 +74,24 @@ def stage0_report(M: int, N: int, res: dict, seconds: float, extras: bool = True
     return "\n".join(lines)
 
 
+STAGE1_RULE = "-" * 56
+
+
+def stage1_banner(M: int, N: int) -> str:
+    """The block the OpenMP program prints before its thread sweep (S1:208-210)."""
+    return "\n".join(["--- (Variant 9: Ellipse x^2 + 4y^2 < 1, OpenMP Test) ---", f"Grid: M={M}, N={N}", STAGE1_RULE])
+
+
 def stage1_report(M: int, N: int, threads: int, res: dict, delta: float, seconds: float) -> str:
+    """One entry of the thread sweep (S1:192, S1:221-223); like stage 0 it prints the symbol, not delta's value."""
     lines = []
     if res.get("status", 1) == 1:
-        lines.append(converged_line(res["iters"], delta))
+        lines.append(converged_line(res["iters"], delta, stage0=True))
     lines.append("Threads = %2d | Time = %.3f s" % (threads, seconds))
     return "\n".join(lines)
+
+
+def stage1_program(M: int, N: int, entries: list) -> str:
+    """Whole stdout of the OpenMP program: banner, one block per (threads, res, seconds) entry, closing rule (S1:226)."""
+    body = [stage1_report(M, N, t, res, 0.0, sec) for t, res, sec in entries]
+    return "\n".join([stage1_banner(M, N), *body, STAGE1_RULE])

@@ -21,10 +21,21 @@ def test_cli_stage0_format():
     assert re.fullmatch(r"M=40, N=40 \| Iter=61 \| Time=\d+\.\d{4} s", out[1])
 
 
+def test_cli_stage0_without_arguments_runs_the_reference_grids():
+    out = _cli("--stage", 0, "--quiet-extras").stdout.splitlines()
+    assert [ln for ln in out if ln.startswith("Converged")] == [
+        f"Converged after {k} iterations (||w(k+1)-w(k)|| < δ)." for k in (17, 31, 61)]
+    assert [ln.split(" | Time")[0] for ln in out if ln.startswith("M=")] == [
+        "M=10, N=10 | Iter=17", "M=20, N=20 | Iter=31", "M=40, N=40 | Iter=61"]
+
+
 def test_cli_stage1_format():
-    out = _cli("--stage", 1, "--threads", 1, 40, 40, "--quiet-extras").stdout.splitlines()
-    assert out[0] == "Converged after 50 iterations (||w(k+1)-w(k)|| < 1e-06)."
-    assert re.fullmatch(r"Threads =  1 \| Time = \d+\.\d{3} s", out[1])
+    out = _cli("--stage", 1, "--threads", "1,2", 40, 40, "--quiet-extras").stdout.splitlines()
+    assert out[:3] == ["--- (Variant 9: Ellipse x^2 + 4y^2 < 1, OpenMP Test) ---", "Grid: M=40, N=40", "-" * 56]
+    assert out[3] == out[5] == "Converged after 50 iterations (||w(k+1)-w(k)|| < δ)."
+    assert re.fullmatch(r"Threads =  1 \| Time = \d+\.\d{3} s", out[4])
+    assert re.fullmatch(r"Threads =  2 \| Time = \d+\.\d{3} s", out[6])
+    assert out[7] == "-" * 56
 
 
 def test_cli_single_positional_argument_is_ignored():

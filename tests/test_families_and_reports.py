@@ -1,7 +1,7 @@
 """Solver families (the reference's stages) and their exact stdout formats."""
 import re
 
-from poisson_ellipse_openmp_mpi_cuda_b200.models import FAMILIES, run_family
+from poisson_ellipse_openmp_mpi_cuda_b200.models import FAMILIES, REFERENCE_PROGRAMS, run_family, run_program
 from poisson_ellipse_openmp_mpi_cuda_b200.utils import report
 
 
@@ -16,7 +16,7 @@ def test_stage0_family_text():
 def test_stage1_and_stage2_family_text():
     res, text = run_family("stage1", 40, 40, threads=1)
     assert res["iters"] == 50
-    assert text.splitlines()[0] == "Converged after 50 iterations (||w(k+1)-w(k)|| < 1e-06)."
+    assert text.splitlines()[0] == "Converged after 50 iterations (||w(k+1)-w(k)|| < δ)."  # S1:192 prints the symbol
     assert re.fullmatch(r"Threads =  1 \| Time = \d+\.\d{3} s", text.splitlines()[1])
     res, text = run_family("stage2", 20, 20)
     lines = text.splitlines()
@@ -25,6 +25,29 @@ def test_stage1_and_stage2_family_text():
     assert re.fullmatch(r"M=20, N=20 \| Iter=26 \| Time=\d+\.\d{6} s", lines[2])
     _, text3 = run_family("stage3", 20, 20, threads=2)
     assert text3.splitlines()[0] == "MPI/OpenMP run with 1 MPI processes; M=20, N=20"
+
+
+def test_stage0_program_sweeps_the_reference_grids():
+    assert REFERENCE_PROGRAMS["stage0"]["grids"] == [(10, 10), (20, 20), (40, 40)]  # S0:177
+    results, text = run_program("stage0")
+    assert [r["iters"] for r in results] == [17, 31, 61]
+    lines = text.splitlines()
+    assert len(lines) == 6
+    for k, (g, it) in enumerate(((10, 17), (20, 31), (40, 61))):
+        assert lines[2 * k] == f"Converged after {it} iterations (||w(k+1)-w(k)|| < δ)."
+        assert re.fullmatch(rf"M={g}, N={g} \| Iter={it} \| Time=\d+\.\d{{4}} s", lines[2 * k + 1])
+
+
+def test_stage1_program_prints_banner_sweep_and_rule():
+    assert REFERENCE_PROGRAMS["stage1"] == {"grid": (800, 1200), "threads": [4, 8, 16, 32]}  # S1:204, S1:213
+    results, text = run_program("stage1-v1", threads=[1, 2])
+    assert [r["iters"] for r in results] == [50, 50]
+    lines = text.splitlines()
+    assert lines[:3] == ["--- (Variant 9: Ellipse x^2 + 4y^2 < 1, OpenMP Test) ---", "Grid: M=40, N=40", "-" * 56]
+    assert lines[3] == lines[5] == "Converged after 50 iterations (||w(k+1)-w(k)|| < δ)."
+    assert re.fullmatch(r"Threads =  1 \| Time = \d+\.\d{3} s", lines[4])
+    assert re.fullmatch(r"Threads =  2 \| Time = \d+\.\d{3} s", lines[6])
+    assert lines[7] == "-" * 56 and len(lines) == 8
 
 
 def test_stage4_report_is_verbatim():
