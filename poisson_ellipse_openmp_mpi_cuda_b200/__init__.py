@@ -6,6 +6,6 @@ Layout:  ``models``  problem definition and the solver families (CPU stages, GPU
          ``parallel`` decomposition, multi-GPU fabric (CUDA IPC peer memory), library-collective solvers
          ``utils``   reports in the reference's formats, solution dumps
 """
-from .api import PoissonSolver, clear_cache, solve  # noqa: F401
+from .api import PoissonSolver, clear_cache, get_solver, solve  # noqa: F401
 
 __version__ = "0.1.0"

@@ -137,6 +137,17 @@ class PoissonSolver:
 _CACHE: dict = {}
 
 
+def get_solver(M: int, N: int, backend: str = "auto", grid=None, threads: int = 1, gpus: int | None = None):
+    """The cached :class:`PoissonSolver` that :func:`solve` uses for these arguments (created on first use)."""
+    if gpus is not None and gpus > 1 and backend in ("auto", "fused") and world_info()[1] == 1:
+        backend = "group"  # several GPUs, one process
+    key = (M, N, backend, str(grid), threads, gpus, world_info())
+    solver = _CACHE.get(key)
+    if solver is None:
+        solver = _CACHE[key] = PoissonSolver(M, N, backend, grid, threads, gpus)
+    return solver
+
+
 def solve(M: int, N: int, backend: str = "auto", grid=None, norm: str = "weighted", delta: float = 1e-6,
           max_iter: int | None = None, threads: int = 1, dump: str | None = None, return_solution: bool = False,
           gpus: int | None = None, **kw):
@@ -145,12 +156,7 @@ def solve(M: int, N: int, backend: str = "auto", grid=None, norm: str = "weighte
     Returns the report dict, or ``(report, w)`` with ``return_solution=True``.  Solvers are cached per
     ``(M, N, backend, grid, threads)`` so repeated calls reuse device memory and peer mappings.
     """
-    if gpus is not None and gpus > 1 and backend in ("auto", "fused") and world_info()[1] == 1:
-        backend = "group"  # several GPUs, one process
-    key = (M, N, backend, str(grid), threads, gpus, world_info())
-    solver = _CACHE.get(key)
-    if solver is None:
-        solver = _CACHE[key] = PoissonSolver(M, N, backend, grid, threads, gpus)
+    solver = get_solver(M, N, backend, grid, threads, gpus)
     res = solver.solve(norm=norm, delta=delta, max_iter=max_iter, **kw)
     w = None
     if dump or return_solution:
