@@ -115,7 +115,7 @@ def run_ours(a) -> dict:
             dist.barrier()
             torch.cuda.synchronize()
 
-    kw = dict(div=a.div, tile_rows=a.tile_rows)
+    kw = dict(div=a.div, tile_rows=a.tile_rows, ap_mode=a.ap_mode)
     for _ in range(a.warmup):
         flush.fill_(1)
         res = solver.solve(**kw)
@@ -163,7 +163,7 @@ def run_ours(a) -> dict:
                    "global_batch": 1, "seq_len": nodes, "parallelism": f"{solver.grid[0]}x{solver.grid[1]} spatial "
                    "blocks, peer-memory halo + in-kernel reductions", "l2": "512 MiB flush buffer written between "
                    "timed solves; each solve re-assembles all arrays", "method": "persistent cooperative kernel",
-                   "div": a.div, "ctas_per_rank": info["ctas_per_rank"]},
+                   "div": a.div, "ap_mode": a.ap_mode, "ctas_per_rank": info["ctas_per_rank"]},
         "samples": dev_s, "iterations": iters[-1], "expected_iterations": EXPECTED_ITERS.get((M, N)), "status": res["status_name"],
         "us_per_iter": us_iter, "l2_error_in_D": res["l2_in_D"], "max_error": res["max_abs"],
         "hbm_gbs_moved_per_gpu": 80.0 * nodes / (us_iter * 1e-6) / 1e9 / world,  # 80 B/node/iteration with coefficient classes
@@ -259,6 +259,8 @@ def main():
                     help="stencil divisions by h1/h2: markstein = correctly rounded 3-instruction sequence (same "
                          "bits as 'true'), true = IEEE division, recip = multiply by the reciprocal")
     ap.add_argument("--tile-rows", type=int, default=0)
+    ap.add_argument("--ap-mode", type=int, default=0, choices=[0, 1, 2],
+                    help="constant-coefficient tiles: 1 store and reload Ap, 2 recompute it in phase C, 0 library default")
     a = ap.parse_args()
     out = run_reference(a) if a.impl == "reference" else run_ours(a)
     if out is not None:

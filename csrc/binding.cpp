@@ -45,7 +45,7 @@ py::tuple solve(int M, int N, int Px, int Py, const std::string& norm, double de
   opt.norm = norm == "unweighted" ? PB_NORM_UNWEIGHTED : PB_NORM_WEIGHTED;
   opt.delta = delta;
   opt.max_iter = max_iter;
-  opt.exact_div = exact_div ? 1 : 0;
+  opt.exact_div = exact_div ? 2 : 0;  // 2 = Markstein sequence, bit-identical to IEEE division
   opt.error_report = 1;
   pb_stats st{};
   if (pb_solver_solve(s, &opt, stream.stream(), &st) != 0)

@@ -82,7 +82,7 @@ int main(int argc, char** argv) {
   opt.norm = PB_NORM_WEIGHTED;
   opt.delta = 1e-6;
   opt.max_iter = -1;
-  opt.exact_div = 1;
+  opt.exact_div = 2;  // Markstein sequence: the bits of IEEE division at a quarter of the instructions
   opt.error_report = 1;
   bool norm_set = false;
 

@@ -7,7 +7,9 @@
 //     phase AB: r, p_old boxes of (TX+2) x (TY+4) (tile + ring; one more column on each side because a box
 //               must start on a 16-byte boundary) and, for tiles with non-constant coefficients, the D box
 //               of the same shape, the a box (TX+1) x TY and the b box TX x (TY+2)
-//     phase C : w, p, r, Ap boxes of TX x TY (+ the D box for tiles with non-constant coefficients)
+//     phase C : w, p, r, Ap boxes of TX x TY (+ the D box for tiles with non-constant coefficients); with
+//               `recompute_ap`, full constant-coefficient tiles load w, r and the (TX+2) x (TY+4) box of p_new
+//               instead and evaluate the stencil a second time, so Ap is neither stored nor reloaded for them
 // so one SM keeps S-1 complete tiles (up to 88 KB each) in flight without spending registers on it, which is
 // what a bandwidth-bound fp64 stencil needs on a part with ~40 KB/SM of latency-bandwidth product.
 // The TMA unit also does the address generation for the misaligned ring boxes and zero-fills the part of
@@ -46,8 +48,10 @@ struct TmaCfg {
   static constexpr int kOffR = 0, kOffP = kExtBytes, kOffD = 2 * kExtBytes, kOffA = 3 * kExtBytes;
   static constexpr int kOffB = 3 * kExtBytes + kABytes;
   static constexpr int kOffCD = 4 * kTileBytes;
+  static constexpr int kOffCPe = 3 * kTileBytes;  // phase C with recomputed Ap: w | - | r | p_new (tile + ring)
   static constexpr int kStageAB = 3 * kExtBytes + kABytes + kBBytes;
   static constexpr int kStageC = 5 * kTileBytes;
+  static_assert(kOffCPe + kExtBytes <= kStageC, "recompute layout must fit into a phase-C stage");
   static constexpr int kStageBytes = kStageAB > kStageC ? kStageAB : kStageC;
   static constexpr int kStages = TX >= 32 ? 2 : 4;
   // transaction bytes = full boxes, out-of-bounds parts included
@@ -55,13 +59,15 @@ struct TmaCfg {
   static constexpr uint32_t kTxABCoef = 1u * ER * EC * 8u + (uint32_t)kABytes + (uint32_t)kBBytes;  // D, a, b
   static constexpr uint32_t kTxCCore = 4u * (uint32_t)kTileBytes;                                // w, p, r, Ap
   static constexpr uint32_t kTxCCoef = (uint32_t)kTileBytes;                                     // D
+  static constexpr uint32_t kTxCRecomp = 2u * (uint32_t)kTileBytes + 1u * ER * EC * 8u;          // w, r, p_new + ring
   static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 128;
   static_assert(kSmemBytes <= 227 * 1024, "stages do not fit into shared memory");
 };
 
 template <int TX, int DIV, bool CC>
 __global__ void __launch_bounds__(kThreads, 1)
-pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints) {
+pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints,
+                          int recompute_ap) {
   using Cfg = TmaCfg<TX>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
@@ -154,6 +160,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     __syncthreads();
   }
   auto tile_mode = [&](int j) -> int { return (CC && j < kMaxTileClass) ? (int)s_tclass[j] : 2; };
+  // Full tiles with constant coefficients can get Ap in phase C by evaluating the stencil again on the p_new box
+  // (the same device function on the same operands: the same bits), which saves the store and the reload of Ap.
+  auto tile_recomputes = [&](int j, int li0, int lj0) -> bool {
+    return recompute_ap && tile_mode(j) != 2 && li0 + TX - 1 <= c.nx && lj0 + TY - 1 <= c.ny;
+  };
 
   // Halo rows travel as LL records (payload32 | sequence32 word pairs, see ctx.h): the producer needs no fence and
   // no counter, the consumer recognises complete values by their sequence number.  Round k of this launch
@@ -239,23 +250,35 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     issue_ab_part(j, n_issued % S, pbuf, true, true, rounds);
     ++n_issued;
   };
-  auto issue_c = [&](int j, int pbuf) {
+  // Phase-C loads of tile j into stage `st`.  part 1 = what this CTA itself wrote or owns (arms the barrier with
+  // the full byte count); part 2 = the p_new box with its ring for a tile that recomputes Ap: the ring cells
+  // were written by other CTAs during phase AB, so that box has to wait for the reduction after it.
+  auto issue_c_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2) {
     if (threadIdx.x == 0) {
       int li0, lj0;
       tile_origin(j, li0, lj0);
-      const unsigned int st = n_issued % S;
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
       const bool coef = tile_mode(j) == 2;
-      fence_proxy_async_smem();
-      mbar_arrive_expect_tx(bar, Cfg::kTxCCore + (coef ? Cfg::kTxCCoef : 0u));
+      const bool recomp = tile_recomputes(j, li0, lj0);
       const int x = kColOff + lj0, y = li0;
-      tma_load_2d_hint(sb, maps + kMapW, x, y, bar, pol_stream);
-      tma_load_2d_hint(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar, pol_keep);
-      tma_load_2d_hint(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar, pol_keep);
-      tma_load_2d_hint(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar, pol_stream);
-      if (coef) tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapD, x, y, bar, pol_keep);
+      if (part1) {
+        fence_proxy_async_smem();
+        mbar_arrive_expect_tx(bar, recomp ? Cfg::kTxCRecomp : Cfg::kTxCCore + (coef ? Cfg::kTxCCoef : 0u));
+        tma_load_2d_hint(sb, maps + kMapW, x, y, bar, pol_stream);
+        tma_load_2d_hint(sb + 2 * Cfg::kTileBytes, maps + kMapR, x, y, bar, pol_keep);
+        if (!recomp) {
+          tma_load_2d_hint(sb + Cfg::kTileBytes, maps + (pbuf ? kMapP1 : kMapP0), x, y, bar, pol_keep);
+          tma_load_2d_hint(sb + 3 * Cfg::kTileBytes, maps + kMapAp, x, y, bar, pol_stream);
+          if (coef) tma_load_2d_hint(sb + Cfg::kOffCD, maps + kMapD, x, y, bar, pol_keep);
+        }
+      }
+      if (part2 && recomp)
+        tma_load_2d_hint(sb + Cfg::kOffCPe, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x - 2, y - 1, bar, pol_keep);
     }
+  };
+  auto issue_c = [&](int j, int pbuf) {
+    issue_c_part(j, n_issued % S, pbuf, true, true);
     ++n_issued;
   };
   bool tma_ok = true;
@@ -337,6 +360,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const int tmode = tile_mode(j);  // CTA-uniform
       const double cf = tmode == 1 ? inv_eps : 1.0;  // uniform tiles: every face coefficient
       const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
+      const bool keep_ap = !tile_recomputes(j, li0, lj0);  // phase C reloads Ap (else it evaluates the stencil again)
 
       // The two halves of the phase on one tile.  `uniform` is a compile-time tag, so the constant-coefficient
       // path carries no shared-memory coefficient loads and the mixed path no selects.
@@ -422,7 +446,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
               b_c = sb2[q * kRows * BC], b_jp = sb2[q * kRows * BC + 1];
             }
             v[q] = stencil_value<DIV>(K, pc[q], s[-EC], s[EC], s[-1], s[1], a_c, a_ip, b_c, b_jp);
-            ap[q * gstep] = v[q];
+            if (keep_ap) ap[q * gstep] = v[q];
           }
 #pragma unroll
           for (int q = 0; q < kPer; ++q) acc_ab = fma(v[q], pc[q], acc_ab);  // same order as the generic loop
@@ -443,9 +467,14 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     }
     if (!tma_ok) break;
     // Prefetch for phase C: it reads only what this CTA itself wrote (p_new, Ap) or owns (w, r, D), so its
-    // first tiles can be in flight while the reduction below waits for the slowest CTA / GPU.
+    // first tiles can be in flight while the reduction below waits for the slowest CTA / GPU.  The exception is
+    // the p_new box with ring of a tile that recomputes Ap (part 2, issued right after the reduction).
+    const unsigned int c_pre_base = n_issued;
     if (threadIdx.x == 0) fence_proxy_async();  // our generic-proxy global stores -> TMA reads
-    for (int j = 0; j < npre; ++j) issue_c(j, cur ^ 1);
+    for (int j = 0; j < npre; ++j) {
+      issue_c_part(j, n_issued % S, cur ^ 1, true, false);
+      ++n_issued;
+    }
     PB_STAMP(t_ab);
     {
       double v[1] = {acc_ab};
@@ -453,6 +482,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       arrive_target += ncta;
       const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
       PB_STAMP(t_r1);
+      // part 2 of the prefetch: every CTA's p_new is complete and acquired (issued on every path, the barriers
+      // of these stages are already armed for the bytes)
+      if (recompute_ap) {
+        if (threadIdx.x == 0) fence_proxy_async();
+        for (int j = 0; j < npre; ++j) issue_c_part(j, (c_pre_base + j) % S, cur ^ 1, false, true);
+      }
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
         break;
@@ -475,6 +510,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
       const double* s_Ap = reinterpret_cast<const double*>(sb + 3 * Cfg::kTileBytes);
       const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffCD);
+      const double* s_pe = reinterpret_cast<const double*>(sb + Cfg::kOffCPe);  // p_new with ring (recompute only)
       int li0, lj0;
       tile_origin(j, li0, lj0);
       const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
@@ -482,17 +518,32 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const bool full = (cx == TX) && (cy == TY);
       const int tmode = tile_mode(j);  // CTA-uniform
       const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
+      const double cf = tmode == 1 ? inv_eps : 1.0;
+      const bool recomp = tile_recomputes(j, li0, lj0);  // CTA-uniform; implies full and constant coefficients
       const bool edge_tile = has_nbr && (li0 == 1 || li0 + cx - 1 == c.nx || lj0 == 1 || lj0 + cy - 1 == c.ny);
       auto run_tile = [&](auto uniform) {
         constexpr bool U = decltype(uniform)::value;
+        // p_new and Ap of the node in tile row `row` (0-based): reloaded, or the stencil of phase AB again
+        auto p_and_ap = [&](int row, double& pc, double& ap) {
+          if (U && recomp) {
+            const double* s = s_pe + (row + 1) * EC + col + 2;
+            pc = s[0];
+            ap = stencil_value<DIV>(K, pc, s[-EC], s[EC], s[-1], s[1], cf, cf, cf, cf);
+          } else {
+            pc = s_p[row * TY + col];
+            ap = s_Ap[row * TY + col];
+          }
+        };
         // loads and arithmetic of one node; stores and halo stores included
         auto c_node = [&](int row, double& dw, double& z, double& rn) {
           const int e = row * TY + col;
           const int li = li0 + row, lj = lj0 + col;
           const size_t g = (size_t)li * S_pitch + (lj + kColOff);
+          double pc, ap;
+          p_and_ap(row, pc, ap);
           const double w_old = s_w[e];
-          const double w_new = fma(alpha, s_p[e], w_old);
-          const double r_new = fma(-alpha, s_Ap[e], s_r[e]);
+          const double w_new = fma(alpha, pc, w_old);
+          const double r_new = fma(-alpha, ap, s_r[e]);
           if (l2_hints)
             __stcs(&c.w[g], w_new);  // streaming store: w is not read again before the next iteration's phase C
           else
@@ -528,9 +579,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 #pragma unroll
           for (int q = 0; q < kPer; ++q) {
             const int e = e0 + q * kRows * TY;
+            double pc, ap;
+            p_and_ap(r00 + q * kRows, pc, ap);
             const double w_old = s_w[e];
-            const double w_new = fma(alpha, s_p[e], w_old);
-            rn[q] = fma(-alpha, s_Ap[e], s_r[e]);
+            const double w_new = fma(alpha, pc, w_old);
+            rn[q] = fma(-alpha, ap, s_r[e]);
             if (l2_hints)
               __stcs(pw + q * gstep, w_new);
             else
@@ -636,30 +689,33 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 // ---------------------------------------------------------------------------------------------------
 template <int TX, int DIV, bool CC>
 static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int l2_hints,
-                                  cudaStream_t stream) {
+                                  int recompute_ap, cudaStream_t stream) {
   const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV, CC>;
   const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints};
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints, (void*)&recompute_ap};
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
 }
 
 template <int TX, bool CC>
 static cudaError_t launch_div(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int div, int l2_hints,
-                              cudaStream_t stream) {
-  if (div == kDivTrue) return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, stream);
-  if (div == kDivMarkstein) return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, stream);
-  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, stream);
+                              int recompute_ap, cudaStream_t stream) {
+  if (div == kDivTrue)
+    return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, stream);
+  if (div == kDivMarkstein)
+    return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, stream);
+  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, stream);
 }
 
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
-                                  int l2_hints, bool compressed, cudaStream_t stream) {
+                                  int l2_hints, bool compressed, bool recompute_ap, cudaStream_t stream) {
+  const int ra = (compressed && recompute_ap) ? 1 : 0;  // without coefficient classes no tile is known to be constant
   if (tile_rows == 32)
-    return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, stream)
-                      : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, stream);
-  return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, stream)
-                    : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, stream);
+    return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, stream)
+                      : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, stream);
+  return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, stream)
+                    : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, stream);
 }
 
 // Debug / unit-test probe: one box load through a tensor map at (x, y) into shared memory, copied out to

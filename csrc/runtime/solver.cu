@@ -28,6 +28,7 @@ Solver::Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int dev
     throw std::runtime_error("Solver: local rank range outside the process grid");
   PB_CUDA_CHECK(cudaSetDevice(device_));
   PB_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_));
+  PB_CUDA_CHECK(cudaDeviceGetAttribute(&l2_bytes_, cudaDevAttrL2CacheSize, device_));
   peer_base_.assign(nranks(), nullptr);
   for (int l = 0; l < nlocal; ++l) {
     blocks_.push_back(make_local_block(M, N, pg_, first_rank + l));

@@ -25,6 +25,7 @@ struct SolveOptions {
   int ctas_per_sm = 0;      // 0 = auto
   int error_report = 1;
   int compressed = 1;       // TMA kernel: coefficient classes (1 byte/cell) instead of streaming a, b, D
+  int ap_mode = 0;          // TMA kernel, uniform tiles: 1 store + reload Ap, 2 recompute it in phase C, 0 = default
   int l2_hints = 0;         // TMA loads carry L2 eviction priorities (helps ~2 % when the working set ~ L2 size)
   int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages) or 16 (4 stages); 0 = auto
   double watchdog_s = 0.0;  // 0 = default (20 s)
@@ -77,6 +78,7 @@ class Solver {
 
   int last_ctas_per_rank() const { return last_ctas_per_rank_; }
   long long last_launches() const { return last_launches_; }
+  bool ap_recompute(int ap_mode) const;  // resolves pb_solve_options.ap_mode (0 = by working-set size)
   size_t h2d_bytes_per_solve() const { return sizeof(DeviceOptions) * blocks_.size(); }
   size_t d2h_bytes_per_solve() const { return sizeof(Control) * blocks_.size(); }
 
@@ -102,6 +104,7 @@ class Solver {
   Control* pinned_ctl_ = nullptr;
   cudaEvent_t ev_[4];
   int sm_count_ = 148;
+  int l2_bytes_ = 126 << 20;
   int last_ctas_per_rank_ = 0;
   int last_method_ = 0;
   long long last_launches_ = 0;

@@ -10,6 +10,17 @@
 
 namespace pb {
 
+// How phase C gets Ap on constant-coefficient tiles.  Evaluating the stencil again instead of storing and
+// reloading Ap trades 16 B/node/iteration for one more stencil evaluation: measured -9 % to -12 % per
+// iteration once the arrays an iteration touches (w, r, p, p', Ap) no longer fit into L2 (3.1 M ... 67 M nodes
+// per GPU), +3.5 % when they do (2.1 M nodes and below: the phase is latency-bound there, not byte-bound).
+bool Solver::ap_recompute(int ap_mode) const {
+  if (ap_mode != 0) return ap_mode == 2;
+  size_t touched = 0;
+  for (const LocalBlock& b : blocks_) touched += (size_t)(b.nx + 2) * (size_t)b.pitch * sizeof(double) * 5;
+  return touched > (size_t)l2_bytes_ / 5 * 4;
+}
+
 void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   if (!fabric_complete_) throw std::runtime_error("persistent solve needs every rank's arena (open_peer) first");
   const int exact = opt.exact_div;
@@ -30,7 +41,7 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   }
   if (tma)
     PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact,
-                                        opt.l2_hints, opt.compressed != 0, stream));
+                                        opt.l2_hints, opt.compressed != 0, ap_recompute(opt.ap_mode), stream));
   else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;

@@ -120,6 +120,9 @@ typedef struct pb_solve_options {
   double watchdog_s;  /* 0 = default (20 s): device-side waits give up after this long */
   int l2_hints;       /* 1: TMA loads carry L2 eviction priorities (keep r, D, p; stream a, b, w, Ap) */
   int full_coefficients; /* 1: stream a, b, D as fp64 boxes instead of the 1-byte coefficient classes (A/B testing) */
+  int ap_mode;        /* TMA persistent kernel, constant-coefficient tiles: 1 = phase AB stores Ap and phase C reloads
+                         it; 2 = phase C recomputes Ap from the p box (same bits, 16 B/node less traffic);
+                         0 = the library's default */
 } pb_solve_options;
 
 int pb_cuda_device_count(void);

@@ -78,6 +78,7 @@ class SolveOptions(C.Structure):
         ("watchdog_s", C.c_double),
         ("l2_hints", C.c_int),
         ("full_coefficients", C.c_int),
+        ("ap_mode", C.c_int),
     ]
 
 

@@ -206,6 +206,23 @@ def test_coefficient_classes_are_bit_identical_to_streamed_coefficients(pg, tile
         s.close()
 
 
+@pytest.mark.parametrize("pg", [(1, 1), (2, 2), (3, 1)])
+@pytest.mark.parametrize("tile_rows", [32, 16])
+def test_recomputed_Ap_is_bit_identical_to_stored_Ap(pg, tile_rows):
+    """ap_mode=2 (phase C evaluates the stencil again on full constant-coefficient tiles instead of reloading Ap)
+    must give the same iteration count, the same stop norm and the same bits as ap_mode=1."""
+    for grid in [(96, 200), (400, 600)]:
+        s = _solver(*grid, *pg)
+        ra = s.solve(tile_rows=tile_rows, ap_mode=1)
+        wa = s.solution_host().clone()
+        rb = s.solve(tile_rows=tile_rows, ap_mode=2)
+        wb = s.solution_host()
+        assert ra["iters"] == rb["iters"] and rb["status"] == 1
+        assert ra["diff_norm"] == rb["diff_norm"]
+        assert torch.equal(wa, wb)
+        s.close()
+
+
 def test_class_bytes_match_arrays(native):
     s = _solver(200, 300).finalize()
     s.step("assemble")
