@@ -148,7 +148,10 @@ def run_ours(a) -> dict:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e_s.append(dt.item())
     clocks = sampler.finish() if sampler else None
-    info = solver._impl.solver.info() if world > 1 else solver._impl.info()
+    gpu_solver = solver._impl.solver if world > 1 else solver._impl
+    info = gpu_solver.info()
+    recomputes = gpu_solver.recomputes_ap(a.ap_mode)
+    bytes_node = 64.0 if recomputes else 80.0
     value = sum(dev_s) / len(dev_s)
     e2e = sum(e2e_s) / len(e2e_s)
     us_iter = 1e6 * res["t_iterations"] / max(1, res["iters"])
@@ -163,10 +166,12 @@ def run_ours(a) -> dict:
                    "global_batch": 1, "seq_len": nodes, "parallelism": f"{solver.grid[0]}x{solver.grid[1]} spatial "
                    "blocks, peer-memory halo + in-kernel reductions", "l2": "512 MiB flush buffer written between "
                    "timed solves; each solve re-assembles all arrays", "method": "persistent cooperative kernel",
-                   "div": a.div, "ap_mode": a.ap_mode, "ctas_per_rank": info["ctas_per_rank"]},
+                   "div": a.div, "ap_mode": a.ap_mode, "ap_recomputed": recomputes, "ctas_per_rank": info["ctas_per_rank"]},
         "samples": dev_s, "iterations": iters[-1], "expected_iterations": EXPECTED_ITERS.get((M, N)), "status": res["status_name"],
         "us_per_iter": us_iter, "l2_error_in_D": res["l2_in_D"], "max_error": res["max_abs"],
-        "hbm_gbs_moved_per_gpu": 80.0 * nodes / (us_iter * 1e-6) / 1e9 / world,  # 80 B/node/iteration with coefficient classes
+        # DRAM bytes per node and iteration on constant-coefficient tiles: r, p, p' | w, r, p', w', r' (64) when
+        # phase C recomputes Ap, 16 more (Ap written and read) when it is stored
+        "hbm_gbs_moved_per_gpu": bytes_node * nodes / (us_iter * 1e-6) / 1e9 / world, "bytes_per_node_iter": bytes_node,
         "wall_s_timed_region": t_wall,
         "e2e": {"value": e2e, "unit": "s", "samples": e2e_s, "h2d_bytes_per_step": info["h2d_bytes"], "d2h_bytes_per_step": info["d2h_bytes"],
                 "what": "poisson_b200.solve(M, N): options pinned->device, assembly, PCG, error report, result "

@@ -1,3 +1,8 @@
+"""Where recomputing Ap in phase C starts to pay (development aid): stored vs recomputed per block size.
+
+One JSON line per grid: [us/iteration, phase AB, phase C, reduction 1, reduction 2] for ap_mode 1 and 2, best of 2,
+200 iterations.  The default rule in Solver::ap_recompute (five arrays > 80 % of L2) comes from this sweep.
+"""
 import json, sys
 import torch
 sys.path.insert(0, ".")

@@ -129,6 +129,8 @@ int pb_solver_info(pb_solver* s, int* ctas, long long* launches, long long* h2d,
   return 0;
 }
 
+int pb_solver_ap_recompute(pb_solver* s, int ap_mode) { return s->impl.ap_recompute(ap_mode) ? 1 : 0; }
+
 // ---- single-process multi-GPU group ----
 pb_group* pb_group_create(int M, int N, int Px, int Py, const int* devices, int ndevices) {
   try {

@@ -127,6 +127,10 @@ class GpuSolver:
         return {"ctas_per_rank": ctas.value, "launches": launches.value, "h2d_bytes": h2d.value,
                 "d2h_bytes": d2h.value}
 
+    def recomputes_ap(self, ap_mode: int = 0) -> bool:
+        """Whether a solve with this ``ap_mode`` recomputes Ap in phase C (0 = decided by working-set size vs L2)."""
+        return bool(self.lib.pb_solver_ap_recompute(self._h, int(ap_mode)))
+
     # -- solve ----------------------------------------------------------------------------------
     def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
               exact_div: bool | None = None, ctas_per_sm: int = 0, error_report: bool = True,
