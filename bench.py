@@ -267,9 +267,16 @@ def main():
     ap.add_argument("--ap-mode", type=int, default=0, choices=[0, 1, 2],
                     help="constant-coefficient tiles: 1 store and reload Ap, 2 recompute it in phase C, 0 library default")
     a = ap.parse_args()
+    # The contract is ONE JSON line on stdout.  Libraries (NCCL with NCCL_DEBUG=VERSION, the reference program's
+    # launcher) write to file descriptor 1 behind Python's back, so everything but the final line goes to stderr.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     out = run_reference(a) if a.impl == "reference" else run_ours(a)
+    sys.stdout.flush()
     if out is not None:
-        print(json.dumps(out), flush=True)
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
+    os.close(json_fd)
 
 
 if __name__ == "__main__":
