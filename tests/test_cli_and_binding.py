@@ -29,6 +29,12 @@ def test_cli_stage0_without_arguments_runs_the_reference_grids():
         "M=10, N=10 | Iter=17", "M=20, N=20 | Iter=31", "M=40, N=40 | Iter=61"]
 
 
+def test_cli_stage0_grid_list():
+    out = _cli("--stage", 0, "--grids", "20x20,10x10", "--quiet-extras").stdout.splitlines()
+    assert [ln.split(" | Time")[0] for ln in out if ln.startswith("M=")] == ["M=20, N=20 | Iter=31", "M=10, N=10 | Iter=17"]
+    assert _cli("--stage", 0, "--grids", "20x20,10").returncode == 2  # odd number of extents
+
+
 def test_cli_stage1_format():
     out = _cli("--stage", 1, "--threads", "1,2", 40, 40, "--quiet-extras").stdout.splitlines()
     assert out[:3] == ["--- (Variant 9: Ellipse x^2 + 4y^2 < 1, OpenMP Test) ---", "Grid: M=40, N=40", "-" * 56]
