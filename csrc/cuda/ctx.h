@@ -78,7 +78,8 @@ struct RankCtx {
   unsigned long long* peer_slots[kMaxRanks];
   Control* ctl;
   // halo completion counters: ours (incremented by the neighbours) and, per direction, the neighbour's
-  // counter that our stores into its ring must bump (its opposite direction)
+  // counter that our stores into its ring must bump (its opposite direction).  Used by the plain-load
+  // persistent kernel (persistent.cu) only; the TMA kernel sends halo rows as LL records (halo_ll below)
   unsigned long long* halo_cnt;
   unsigned long long* nbr_halo_cnt[4];
   // Fence-free halo lines (TMA kernel): per direction and parity a line of (payload32 | seq32) word pairs, one pair
