@@ -55,7 +55,12 @@ def run_program(name: str, grids=None, grid=None, threads=None, **kw):
     return [e[1] for e in entries], report.stage1_program(M, N, entries)
 
 
-def run_family(name: str, M: int, N: int, threads: int = 1, grid=None, delta: float = 1e-6, extras: bool = True, **kw):
+def run_family(name: str, M: int, N: int, threads: int = 1, grid=None, delta: float = 1e-6, extras: bool = True,
+               dump: str | None = None, **kw):
+    """Run one stage's equivalent; returns ``(report dict, stdout text in that stage's format)``.
+
+    ``dump`` writes the full nodal field (collective for the distributed stages; rank 0 writes the file).
+    """
     backend, norm, _ = FAMILIES[name]
     rank, world = world_info()
     t_prog = time.perf_counter()
@@ -69,8 +74,15 @@ def run_family(name: str, M: int, N: int, threads: int = 1, grid=None, delta: fl
     elif name == "stage1":
         text = report.stage1_report(M, N, threads, res, delta, res["seconds"])
     elif name in ("stage2", "stage3"):
-        text = report.stage23_report(M, N, world, res, delta, res["seconds"], hybrid=(name == "stage3"))
+        text = report.stage23_report(M, N, world, res, delta, res["seconds"], hybrid=(name == "stage3"), extras=extras)
     else:
-        text = report.stage4_report(M, N, world, res, delta, t_init=t_before - t_prog, t_solver=t_after - t_before)
+        text = report.stage4_report(M, N, world, res, delta, t_init=t_before - t_prog, t_solver=t_after - t_before,
+                                    extras=extras)
+    if dump:
+        from ..utils.dump import write_solution
+
+        w = solver.solution()
+        if rank == 0:
+            write_solution(dump, w, M, N)
     solver.close()
     return res, text
