@@ -129,6 +129,11 @@ int pb_solver_info(pb_solver* s, int* ctas, long long* launches, long long* h2d,
   return 0;
 }
 
+int pb_solver_cta_times(pb_solver* s, int local_idx, double* host_out, int max_ctas) {
+  int n = 0;
+  const int rc = guarded([&] { n = s->impl.cta_times(local_idx, host_out, max_ctas); });
+  return rc != 0 ? rc : n;
+}
 int pb_solver_ap_recompute(pb_solver* s, int ap_mode) { return s->impl.ap_recompute(ap_mode) ? 1 : 0; }
 
 // ---- single-process multi-GPU group ----

@@ -29,6 +29,7 @@ constexpr size_t kArriveOffset = 8192;             // arrival counter (u32) + pa
 constexpr size_t kHaloCntOffset = 8192 + 1024;     // u64[4]: halo tiles received per direction (monotonic)
 constexpr int kPartialStride = 8;                  // doubles per CTA in the partials area
 constexpr size_t kPartialsOffset = 16384;          // [kMaxCtas][kPartialStride] doubles
+constexpr size_t kCtaTimesOffset = 81920;          // [kMaxCtas][4] doubles: per-CTA ns in AB, C, reduction 1, reduction 2
 constexpr size_t kHeaderBytes = 131072;            // arrays start here; r is the first array
 
 // Scalars of the iteration, status and device-side timers.  Lives at the start of the arena.

@@ -109,7 +109,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
   const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
-  const bool timing = (cta == 0 && threadIdx.x == 0);
+  const bool timing = threadIdx.x == 0;  // every CTA keeps its own phase clocks; CTA 0's go into the report
   const int S_pitch = c.pitch;
 
   unsigned int seq = ctl->red_seq, arrive_target = 0;
@@ -664,6 +664,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   if (k > max_iter) k = max_iter;
   drain();
 
+  if (threadIdx.x == 0 && tma_ok) {
+    // where this CTA spent the solve (ns): phase AB, phase C, waiting in reduction 1, waiting in reduction 2
+    double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(ctl) + kCtaTimesOffset) + 4 * cta;
+    mine[0] = (double)t_ab, mine[1] = (double)t_c, mine[2] = (double)t_r1, mine[3] = (double)t_r2;
+  }
   if (cta == 0 && threadIdx.x == 0 && tma_ok) {
     if (ctl->red[2] != 0.0) status = PB_STATUS_WATCHDOG;
     ctl->iter = (int)k;

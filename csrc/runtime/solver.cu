@@ -17,7 +17,8 @@ static_assert(offsetof(Control, watchdog_ns) - offsetof(Control, delta) == offse
               "DeviceOptions must mirror the option block of Control");
 static_assert(sizeof(Control) <= kSlotsOffset, "Control overflows its page");
 static_assert(2 * kMaxRanks * kSlotWords * 8 <= kArriveOffset - kSlotsOffset, "slot area overflows");
-static_assert(kMaxCtas * kPartialStride * 8 <= kHeaderBytes - kPartialsOffset, "partials overflow");
+static_assert(kPartialsOffset + kMaxCtas * kPartialStride * 8 <= kCtaTimesOffset, "partials overflow");
+static_assert(kCtaTimesOffset + kMaxCtas * 4 * 8 <= kHeaderBytes, "per-CTA timers overflow");
 
 Solver::Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int device)
     : grid_(make_grid(M, N)), pg_{Px, Py}, first_rank_(first_rank), device_(device) {

@@ -78,6 +78,7 @@ class Solver {
 
   int last_ctas_per_rank() const { return last_ctas_per_rank_; }
   long long last_launches() const { return last_launches_; }
+  int cta_times(int l, double* host_out, int max_ctas);  // seconds per CTA: AB, C, reduction 1, reduction 2
   bool ap_recompute(int ap_mode) const;  // resolves pb_solve_options.ap_mode (0 = by working-set size)
   size_t h2d_bytes_per_solve() const { return sizeof(DeviceOptions) * blocks_.size(); }
   size_t d2h_bytes_per_solve() const { return sizeof(Control) * blocks_.size(); }

@@ -183,6 +183,15 @@ void Solver::xgpu_bench(int iters, int mode, int edge, int ctas, cudaStream_t st
   out[1] = pinned_ctl_[0].red[0];
 }
 
+int Solver::cta_times(int l, double* host_out, int max_ctas) {
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  const int n = std::min(last_ctas_per_rank_, max_ctas);
+  if (n <= 0) return 0;
+  PB_CUDA_CHECK(cudaMemcpy(host_out, arenas_[l] + kCtaTimesOffset, sizeof(double) * 4 * (size_t)n, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 4 * n; ++i) host_out[i] *= 1e-9;
+  return n;
+}
+
 void Solver::gather_block(int l, double* dev_out, long long ld, cudaStream_t stream) {
   const LocalBlock& b = blocks_[l];
   PB_CUDA_CHECK(launch_gather_interior(array(l, 0), b.nx, b.ny, b.pitch, dev_out, ld, stream));

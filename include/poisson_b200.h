@@ -142,6 +142,9 @@ void* pb_solver_control_err(pb_solver* s, int local_idx); /* device double[5]: e
 int pb_solver_copy_solution(pb_solver* s, double* host_full /* (M+1)*(N+1) */, void* cuda_stream);
 int pb_solver_gather_block(pb_solver* s, int local_idx, void* dev_out, long long ld, void* cuda_stream);
 int pb_solver_info(pb_solver* s, int* ctas_per_rank, long long* launches, long long* h2d_bytes, long long* d2h_bytes);
+/* Per-CTA device clocks of the last persistent (TMA) solve: out[4 * cta + {0,1,2,3}] = seconds in phase AB, phase C,
+   waiting in reduction 1, waiting in reduction 2.  Returns the number of CTAs written (<= max_ctas) or < 0. */
+int pb_solver_cta_times(pb_solver* s, int local_idx, double* host_out, int max_ctas);
 /* 1 if a solve with this ap_mode recomputes Ap in phase C on this solver's blocks (0 resolves by working-set size) */
 int pb_solver_ap_recompute(pb_solver* s, int ap_mode);
 

@@ -126,6 +126,7 @@ def _declare(lib: C.CDLL) -> None:
         "pb_solver_gather_block": (I, [vp, I, vp, LL, vp]),
         "pb_solver_info": (I, [vp, C.POINTER(I), C.POINTER(LL), C.POINTER(LL), C.POINTER(LL)]),
         "pb_solver_ap_recompute": (I, [vp, I]),
+        "pb_solver_cta_times": (I, [vp, I, dp, I]),
         "pb_group_create": (vp, [I, I, I, I, C.POINTER(I), I]),
         "pb_group_destroy": (None, [vp]),
         "pb_group_solve": (I, [vp, C.POINTER(SolveOptions), C.POINTER(Stats)]),

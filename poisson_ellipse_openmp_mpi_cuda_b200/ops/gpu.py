@@ -127,6 +127,15 @@ class GpuSolver:
         return {"ctas_per_rank": ctas.value, "launches": launches.value, "h2d_bytes": h2d.value,
                 "d2h_bytes": d2h.value}
 
+    def cta_times(self, local_idx: int = 0) -> torch.Tensor:
+        """Per-CTA device clocks of the last persistent solve: ``[ctas, 4]`` seconds in phase AB, phase C and
+        waiting in reductions 1 and 2 (a CTA that waits long in a reduction finished its phase early)."""
+        n = self.info()["ctas_per_rank"]
+        out = torch.zeros((max(n, 1), 4), dtype=torch.float64)
+        got = self.lib.pb_solver_cta_times(self._h, local_idx, C.cast(out.data_ptr(), C.POINTER(C.c_double)), n)
+        _native.check(min(got, 0), "pb_solver_cta_times")
+        return out[:max(got, 0)]
+
     def recomputes_ap(self, ap_mode: int = 0) -> bool:
         """Whether a solve with this ``ap_mode`` recomputes Ap in phase C (0 = decided by working-set size vs L2)."""
         return bool(self.lib.pb_solver_ap_recompute(self._h, int(ap_mode)))
