@@ -223,6 +223,17 @@ def test_recomputed_Ap_is_bit_identical_to_stored_Ap(pg, tile_rows):
         s.close()
 
 
+def test_per_cta_clocks():
+    """Every CTA reports where it spent the solve; the four parts add up to (at most) the device time of the loop."""
+    s = _solver(800, 1200)
+    r = s.solve()
+    t = s.cta_times()
+    assert tuple(t.shape) == (r["ctas_per_rank"], 4)
+    assert (t >= 0).all() and t[:, :2].min() > 0
+    assert float(t.sum(dim=1).max()) <= r["t_iterations"] * 1.05
+    s.close()
+
+
 def test_class_bytes_match_arrays(native):
     s = _solver(200, 300).finalize()
     s.step("assemble")
