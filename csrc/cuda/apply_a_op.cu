@@ -105,7 +105,9 @@ extern "C" int pb_apply_A_dot(int M, int N, int nx, int ny, int pitch, const voi
 // Set-up: `g_apply_a_scratch` is a device symbol.  In host code that name is only a stand-in, not a
 // device address, so the first call made on a given device (with that device current) asks the runtime for
 // the real address once, with cudaGetSymbolAddress, checks the result and caches it per device.  Make that
-// first call during initialisation, before any stream capture is begun on the device.
+// first call during initialisation, before any stream capture is begun on the device.  The cached address is
+// never refreshed: cudaDeviceReset destroys the context the array lives in and leaves the cache pointing at
+// freed memory, so this entry point must not be used on a device after it has been reset.
 //
 // Sharing: all calls on a device use the one array, and it keeps whatever the previous call left in it.
 // Nothing in it has to start at zero -- each call writes every per-tile slot it later reads, and reads

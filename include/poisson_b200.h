@@ -184,8 +184,10 @@ int pb_apply_A_dot(int M, int N, int nx, int ny, int pitch, const void* p, const
  * for programs that own all device memory through their own pool, that sit on a path where the driver's
  * allocator lock is not acceptable, or that may not allocate after start-up.  Limit: ceil(nx/32) *
  * ceil(ny/64) <= 65536 tiles, larger blocks return -1 with an explanatory pb_last_error().  The first call
- * on each device looks up the array's device address (do it at start-up, before any stream capture); calls
- * on one device share the array, so calls that overlap on the GPU race -- keep them stream-ordered. */
+ * on each device looks up the array's device address (do it at start-up, before any stream capture) and keeps
+ * it for the life of the process: after a cudaDeviceReset on that device the kept address is stale, so a
+ * program that resets a device must not call this entry point on it again.  Calls on one device share the
+ * array, so calls that overlap on the GPU race -- keep them stream-ordered. */
 int pb_apply_A_dot_noalloc(int M, int N, int nx, int ny, int pitch, const void* p, const void* a, const void* b,
                            void* Ap, void* dot_out, void* cuda_stream);
 

@@ -36,7 +36,6 @@ LIB_SOURCES = [
     "cuda/persistent.cu",
     "cuda/persistent_tma.cu",
     "cuda/apply_a_op.cu",
-    "runtime/fabric.cu",
     "runtime/solver.cu",
     "runtime/solver_run.cu",
     "runtime/group.cu",
@@ -82,7 +81,12 @@ def _compile(src_rel: str, verbose: bool) -> Path:
 
 
 def existing_sources(names):
-    return [s for s in names if (CSRC / s).exists()]
+    """The listed sources; a name that is not on disk is an error (a library silently built without one of its
+    translation units would only fail at load time, on the GPU box)."""
+    missing = [s for s in names if not (CSRC / s).exists()]
+    if missing:
+        raise FileNotFoundError(f"native sources listed in _build.py are missing: {missing}")
+    return list(names)
 
 
 def build_native(verbose: bool = False, force: bool = False) -> Path:

@@ -1,0 +1,129 @@
+"""The persistent TMA kernel against oracles it shares no code with.
+
+* one and two iterations (`max_iter = 1, 2`): w, r, p and Ap as the kernel leaves them in its arrays against a
+  plain PyTorch fp64 evaluation of the same recurrence built from the assembled a, b, D, F -- on a grid with
+  several tiles per CTA (400 x 600: 475 tiles of 32 x 64 on 148 CTAs, so the stage ring wraps, stages are reused
+  and the cross-phase prefetch is exercised) and on 2 x 2 virtual ranks (halo records, ring recomputation);
+* the converged solution element by element against the CPU oracle (csrc/cpu/oracle.cpp) for every combination
+  of tile height and Ap mode;
+* 50 iterations at the headline size (4096 x 4096) against the step kernels.
+The reference's own check is "equal iteration counts" (R4 p.9-12); these tests can fail where that one cannot.
+"""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _solver(*a, **k):
+    from poisson_ellipse_openmp_mpi_cuda_b200.ops.gpu import GpuSolver
+
+    return GpuSolver(*a, **k)
+
+
+def _assembled(M, N):
+    """a, b, D, F of the whole domain as (M+1) x (N+1) fp64 CUDA tensors indexed by node (i, j)."""
+    s = _solver(M, N).finalize()
+    s.step("assemble")
+    torch.cuda.synchronize()
+    co = s.col_off
+    out = {k: s.array(k)[:, co:co + N + 1].clone() for k in ("a", "b", "D", "r")}
+    s.close()
+    return out["a"], out["b"], out["D"], out["r"]
+
+
+def _apply_A(p, a, b, h1, h2):
+    """(A p) on the interior nodes, association of S4:526-535; p is (M+1) x (N+1) with a zero boundary."""
+    c = p[1:-1, 1:-1]
+    ax = -1.0 / h1 * (a[2:, 1:-1] * (p[2:, 1:-1] - c) / h1 - a[1:-1, 1:-1] * (c - p[:-2, 1:-1]) / h1)
+    ay = -1.0 / h2 * (b[1:-1, 2:] * (p[1:-1, 2:] - c) / h2 - b[1:-1, 1:-1] * (c - p[1:-1, :-2]) / h2)
+    out = torch.zeros_like(p)
+    out[1:-1, 1:-1] = ax + ay
+    return out
+
+
+def _torch_pcg(M, N, iters):
+    """`iters` iterations of the recurrence of S4:802-942 in plain PyTorch fp64; returns w, r, p, Ap of the last one."""
+    a, b, D, F = _assembled(M, N)
+    h1, h2 = 2.0 / M, 1.2 / N
+    inner = torch.zeros_like(F, dtype=torch.bool)
+    inner[1:-1, 1:-1] = True
+    Dsafe = torch.where(inner, D, torch.ones_like(D))
+    w = torch.zeros_like(F)
+    r = torch.where(inner, F, torch.zeros_like(F))
+    z = r / Dsafe
+    p = z.clone()
+    zr = (z * r).sum() * h1 * h2
+    Ap = p_used = None
+    for _ in range(iters):
+        Ap = _apply_A(p, a, b, h1, h2)
+        alpha = zr / ((Ap * p).sum() * h1 * h2)
+        w = w + alpha * p
+        r = r - alpha * Ap
+        z = r / Dsafe
+        zr_new = (z * r).sum() * h1 * h2
+        p_used = p
+        p = z + (zr_new / zr) * p
+        zr = zr_new
+    return w, r, p_used, Ap
+
+
+def _close(got, ref, what):
+    scale = float(ref.abs().max())
+    err = float((got - ref).abs().max())
+    assert err <= 1e-13 * scale + 1e-300, f"{what}: max |diff| {err:.3e} against scale {scale:.3e}"
+
+
+@pytest.mark.parametrize("iters", [1, 2])
+@pytest.mark.parametrize("pg", [(1, 1), (2, 2)])
+@pytest.mark.parametrize("tile_rows,ap_mode", [(32, 1), (32, 2), (16, 1)])
+def test_first_iterations_against_pytorch(iters, pg, tile_rows, ap_mode):
+    M, N = 400, 600
+    w_ref, r_ref, p_ref, Ap_ref = _torch_pcg(M, N, iters)
+    s = _solver(M, N, *pg)
+    res = s.solve(max_iter=iters, tile_rows=tile_rows, ap_mode=ap_mode, error_report=False)
+    assert res["iters"] == iters and res["status_name"] == "max_iter"
+    pname = "p1" if iters % 2 else "p0"  # the buffer phase AB of the last iteration wrote
+    for l in range(pg[0] * pg[1]):
+        blk = s.block(l)
+        I, J = slice(blk.i0, blk.i0 + blk.nx), slice(blk.j0, blk.j0 + blk.ny)
+        _close(s.interior("w", l), w_ref[I, J], f"w block {l}")
+        _close(s.interior("r", l), r_ref[I, J], f"r block {l}")
+        _close(s.interior(pname, l), p_ref[I, J], f"p block {l}")
+        if ap_mode == 1:  # with ap_mode 2 full constant-coefficient tiles never store Ap
+            _close(s.interior("Ap", l), Ap_ref[I, J], f"Ap block {l}")
+    s.close()
+
+
+@pytest.mark.parametrize("tile_rows", [32, 16])
+@pytest.mark.parametrize("ap_mode", [1, 2])
+def test_converged_solution_elementwise_against_cpu_oracle(native, tile_rows, ap_mode):
+    M, N = 400, 600
+    ref = torch.zeros((M + 1, N + 1), dtype=torch.float64)
+    st = native.Stats()
+    native.lib().pb_cpu_solve(M, N, 0, 1e-6, -1, 4, 0, ref.data_ptr(), C.byref(st))
+    assert st.iters == 546
+    for pg in [(1, 1), (2, 2)]:
+        s = _solver(M, N, *pg)
+        res = s.solve(tile_rows=tile_rows, ap_mode=ap_mode)
+        assert res["iters"] == 546
+        w = s.solution_host()
+        assert float((w - ref).abs().max()) < 1e-10
+        s.close()
+
+
+def test_headline_grid_50_iterations_against_step_kernels():
+    """4096 x 4096 (the benchmark's grid): 50 iterations of the persistent kernel and of the step kernels (one
+    launch per phase, plain loads, grid-wide reductions by separate kernels) leave the same w and stop norm."""
+    M = N = 4096
+    s = _solver(M, N)
+    ra = s.solve(max_iter=50, error_report=False)
+    wa = s.interior("w").clone()
+    rb = s.solve(method="step_fused", max_iter=50, error_report=False)
+    wb = s.interior("w")
+    assert ra["iters"] == rb["iters"] == 50
+    assert ra["diff_norm"] == pytest.approx(rb["diff_norm"], rel=1e-9)
+    assert float((wa - wb).abs().max()) <= 1e-12 * float(wb.abs().max())
+    s.close()

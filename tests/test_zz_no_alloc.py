@@ -41,6 +41,21 @@ def _call(fn, M, N, blk, p, a, b):
     return rc, Ap, dot
 
 
+def _torch_stencil(M, N, blk, p, a, b):
+    """Ap on the owned nodes and h1 h2 (Ap, p), evaluated with plain PyTorch fp64 arithmetic: an oracle that shares
+    no code with either entry point."""
+    from poisson_ellipse_openmp_mpi_cuda_b200.parallel.decomp import col_offset
+
+    co, h1, h2 = col_offset(), 2.0 / M, 1.2 / N
+    I, J = slice(1, blk.nx + 1), slice(co + 1, co + 1 + blk.ny)
+    Ip, Im = slice(2, blk.nx + 2), slice(0, blk.nx)
+    Jp, Jm = slice(co + 2, co + 2 + blk.ny), slice(co, co + blk.ny)
+    ax = -1.0 / h1 * (a[Ip, J] * (p[Ip, J] - p[I, J]) / h1 - a[I, J] * (p[I, J] - p[Im, J]) / h1)
+    ay = -1.0 / h2 * (b[I, Jp] * (p[I, Jp] - p[I, J]) / h2 - b[I, J] * (p[I, J] - p[I, Jm]) / h2)
+    ref = ax + ay
+    return (I, J), ref, float((ref * p[I, J]).sum()) * h1 * h2
+
+
 def test_noalloc_entry_point_matches_allocating_one(native):
     lib = native.lib()
     torch.cuda.set_device(0)
@@ -49,12 +64,18 @@ def test_noalloc_entry_point_matches_allocating_one(native):
         blk, a, b, p = _inputs(M, N, seed)
         rc_ref, Ap_ref, dot_ref = _call(lib.pb_apply_A_dot, M, N, blk, p, a, b)
         assert rc_ref == 0, native.last_error()
+        (I, J), Ap_torch, dot_torch = _torch_stencil(M, N, blk, p, a, b)
         for _ in range(2):
             rc, Ap, dot = _call(lib.pb_apply_A_dot_noalloc, M, N, blk, p, a, b)
             assert rc == 0, native.last_error()
             assert torch.allclose(Ap, Ap_ref, rtol=1e-13, atol=1e-12)
             assert dot.item() == pytest.approx(dot_ref.item(), rel=1e-12)
             assert dot.item() != 0.0
+            # and against the independent PyTorch evaluation, not only against the sibling entry point (the two
+            # differ by roundings of individual terms of size ~ a/h^2, so the bound is relative to the largest
+            # value, not to each node's own, possibly cancelled, value)
+            assert float((Ap[I, J] - Ap_torch).abs().max()) <= 1e-13 * float(Ap_torch.abs().max())
+            assert dot.item() == pytest.approx(dot_torch, rel=1e-12)
 
 
 def test_noalloc_entry_point_rejects_blocks_beyond_its_scratch(native):
