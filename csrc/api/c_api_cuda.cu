@@ -134,6 +134,14 @@ int pb_solver_cta_times(pb_solver* s, int local_idx, double* host_out, int max_c
   const int rc = guarded([&] { n = s->impl.cta_times(local_idx, host_out, max_ctas); });
   return rc != 0 ? rc : n;
 }
+int pb_solver_cta_report(pb_solver* s, int local_idx, double* host_out, int max_ctas) {
+  int n = 0;
+  const int rc = guarded([&] { n = s->impl.cta_report(local_idx, host_out, max_ctas); });
+  return rc != 0 ? rc : n;
+}
+int pb_solver_tile_counts(pb_solver* s, long long* out3) {
+  return guarded([&] { s->impl.tile_counts(out3); });
+}
 int pb_solver_ap_recompute(pb_solver* s, int ap_mode) { return s->impl.ap_recompute(ap_mode) ? 1 : 0; }
 
 // ---- single-process multi-GPU group ----

@@ -29,8 +29,16 @@ constexpr size_t kArriveOffset = 8192;             // arrival counter (u32) + pa
 constexpr size_t kHaloCntOffset = 8192 + 1024;     // u64[4]: halo tiles received per direction (monotonic)
 constexpr int kPartialStride = 8;                  // doubles per CTA in the partials area
 constexpr size_t kPartialsOffset = 16384;          // [kMaxCtas][kPartialStride] doubles
-constexpr size_t kCtaTimesOffset = 81920;          // [kMaxCtas][4] doubles: per-CTA ns in AB, C, reduction 1, reduction 2
-constexpr size_t kHeaderBytes = 131072;            // arrays start here; r is the first array
+constexpr int kCtaTimeWords = 8;                   // doubles per CTA in the per-CTA report area
+constexpr size_t kCtaTimesOffset = 81920;          // [kMaxCtas][kCtaTimeWords] doubles: ns in AB, C, reduction 1, reduction 2,
+                                                   // tiles by kind (constant coefficients with Ap recomputed / stored, mixed), ns halo wait
+constexpr size_t kLl1Offset = 147456;              // [kRedValues][kMaxCtas][2] u64: per-CTA records of star_sum (CTA -> CTA 0)
+constexpr size_t kResOffset = 180224;              // [kRedValues][2] u64: result record of star_sum (CTA 0 -> every CTA)
+#ifdef PB_VAR_HDR  // experiment only: the round-1 position of the arrays (star_sum's areas then overlap the first array)
+constexpr size_t kHeaderBytes = 131072;
+#else
+constexpr size_t kHeaderBytes = 196608;            // arrays start here; r is the first array
+#endif
 
 // Scalars of the iteration, status and device-side timers.  Lives at the start of the arena.
 struct Control {
@@ -51,6 +59,7 @@ struct Control {
   unsigned long long watchdog_ns;  // 0 = default
   // device timers (ns, accumulated by CTA 0 of the persistent kernel)
   unsigned long long t_ab, t_c, t_red1, t_red2, t_init, t_total;
+  unsigned long long t_halo;  // CTA 0: ns spent waiting for / unpacking the neighbours' halo records (inside t_c)
   // error report partials {sum e^2 in D, sum e^2 all, max |e|, max w, nodes in D}
   double err[5];
 };

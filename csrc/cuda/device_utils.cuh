@@ -42,6 +42,11 @@ __device__ __forceinline__ int ld_relaxed_gpu_s32(const int* p) {
   asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
   unsigned long long v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -55,6 +60,9 @@ __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_re
 // Orders earlier generic-proxy accesses (ours, or ones we acquired from other SMs / GPUs) before later
 // async-proxy (TMA) accesses.
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// the same for global memory only: what every writing thread executes before the barrier that hands its stores to the
+// thread issuing the TMA loads (measured: 44 cycles for a whole CTA)
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
 // Sum over the CTA with a fixed shape (lane tree, then warp 0 tree over the warp sums), so the result
 // does not depend on scheduling.  `scratch` holds NV * 32 doubles.  Result valid in thread 0.
@@ -215,6 +223,330 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
   for (int k = 0; k < kRedValues; ++k) res.v[k] = smem[64 + k];
   res.ok = smem[64 + kRedValues] != 0.0;
   __syncthreads();
+  return res;
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// star_sum: the cross-rank reduction of the TMA kernel.  Same contract as cross_rank_sum (all threads of all CTAs
+// of a rank call it, every rank the same number of times, bit-identical result everywhere), different mechanics:
+// no atomic, no elected "last arriver", only warp 0 of a CTA takes part, and the only line that many SMs poll is
+// polled with one lane and one load per value.  bench/experiments/hop_latency.cu measured the building blocks on a
+// B200: a "store a 16-byte record, another SM polls it" hop costs 0.5 us on an idle line, a GPU-scope fence in front
+// of the store 0.3 us more, 147 writers + one gathering warp + one result record 1.2 us per round (1.9 us with the
+// two fences), records packed 16 bytes apart being the fastest layout; and a two-level tree in which warp 0 of every
+// CTA polled 13 group records with 13 lanes was SLOWER (7.5 us) than cross_rank_sum (4.2 us), because ~150 warps
+// spinning on the same four lines back up the two L2 slices that hold them.  Hence a star:
+//
+//   level 0  CTA sum: lane tree per warp -> shared memory -> one __syncthreads -> lane tree over the warp sums
+//   level 1  lane 0 releases the CTA's global stores with one GPU-scope fence and writes an LL record (each 8-byte
+//            word = 32 bits of payload | sequence number, so the record carries its own validity) into ll1[k][cta]
+//   level 2  warp 0 of CTA 0 looks at all records of the rank at once (lane l reads records l, l+32, ... back to
+//            back, every load of a look in flight together, so the fan-in costs one hop, not one per record) and
+//            adds them in a fixed order.  Several ranks: it stores the rank's record into every rank's slot area
+//            over NVLink, polls its own slot area and adds the ranks' records in rank order.
+//   level 3  the same warp fences and stores the result record; lane 0 of warp 0 of every other CTA polls it (147
+//            such pollers on one line cost nothing measurable; private mailboxes written by CTA 0 were not faster),
+//            then reads it once more as an acquire load.
+//   The result goes through shared memory, second __syncthreads.
+//
+// The fences are the ones the data needs anyway: a reduction is also the grid-wide barrier between the phases (what
+// the CTAs stored before it must be readable by every other CTA after it), and the chain member -> CTA 0 -> member is
+// release / acquire at every link.  No buffer alternates except the slots: a CTA writes record s+1 only after it
+// read result s, which CTA 0 wrote after consuming every record s, and CTA 0 writes result s+1 only after it has
+// seen every record s+1.
+//
+// Replaces dot_gpu + MPI_Allreduce (S4:771-786, S4:871, S4:892, S4:925) like cross_rank_sum, which the plain-load
+// persistent kernel keeps because its halo is published by system-scope fences inside the reduction.
+__device__ __forceinline__ void ld_relaxed_gpu_v2_u64(const unsigned long long* p, unsigned long long& a,
+                                                      unsigned long long& b) {
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_gpu_v2_u64(unsigned long long* p, unsigned long long a, unsigned long long b) {
+  asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ld_relaxed_sys_v2_u64(const unsigned long long* p, unsigned long long& a,
+                                                      unsigned long long& b) {
+  asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_v2_u64(unsigned long long* p, unsigned long long a, unsigned long long b) {
+  asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+
+__device__ __forceinline__ void ll_encode(double v, unsigned int seq, unsigned long long& w0, unsigned long long& w1) {
+  const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+  w0 = (bits & 0xffffffffull) | ((unsigned long long)seq << 32);
+  w1 = (bits >> 32) | ((unsigned long long)seq << 32);
+}
+__device__ __forceinline__ double ll_decode(unsigned long long w0, unsigned long long w1) {
+  return __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+}
+
+// One look at NV LL values, `stride` u64 apart: true when every word carries `seq` (then `out` holds the values).
+template <int NV, bool SYS>
+__device__ __forceinline__ bool ll_peek(const unsigned long long* rec, size_t stride, unsigned int seq, double (&out)[NV]) {
+  bool all = true;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    unsigned long long w0, w1;
+    if (SYS)
+      ld_relaxed_sys_v2_u64(rec + k * stride, w0, w1);
+    else
+      ld_relaxed_gpu_v2_u64(rec + k * stride, w0, w1);
+    all = all && ((unsigned int)(w0 >> 32) == seq) && ((unsigned int)(w1 >> 32) == seq);
+    out[k] = ll_decode(w0, w1);
+  }
+  return all;
+}
+
+// Poll such a record until it carries `seq` (bounded by `limit` ns).
+template <int NV, bool SYS>
+__device__ __forceinline__ bool ll_poll(const unsigned long long* rec, size_t stride, unsigned int seq,
+                                        unsigned long long limit, double (&out)[NV]) {
+  unsigned long long t0 = 0;
+  unsigned int spins = 0;
+  while (!ll_peek<NV, SYS>(rec, stride, seq, out)) {
+    if ((++spins & 0x3ffu) == 0u) {
+      const unsigned long long now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > limit) return false;
+    }
+  }
+  return true;
+}
+
+// fixed-shape sum over the 32 lanes, result in every lane (xor butterfly: partners hold a + b and b + a, the same bits)
+__device__ __forceinline__ double warp_sum_all(double x) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+  return x;
+}
+
+#ifdef PB_VAR_INLINE  // experiment only
+#define PB_EXCHANGE_INLINE __forceinline__
+#else
+#define PB_EXCHANGE_INLINE __noinline__
+#endif
+#ifdef PB_VAR_NOUNROLL  // experiment only
+constexpr int kGatherUnroll = 0;
+#else
+constexpr int kGatherUnroll = 5;
+#endif
+
+// Levels 1-3 of star_sum, executed by warp 0 of every CTA: tot_io holds the CTA's sums on entry and the global sums
+// on return.  Not inlined on purpose: the gather keeps up to 20 loads in flight and must not cost the tile loops of
+// the calling kernel any registers.
+// TRACE (micro-benchmark only): thread 0 adds the clock64 distance between the numbered steps to trace[3..7].
+template <int NV, bool TRACE>
+__device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_io, unsigned int seq, int cta, int ncta,
+                                                 unsigned long long limit, long long* trace) {
+  const RankCtx& c = *cp;
+  const int lane = threadIdx.x & 31;
+  long long tr_prev = 0;
+  if constexpr (TRACE) tr_prev = clock64();
+#define PB_TRACE(i)                                   \
+  if constexpr (TRACE) {                              \
+    const long long now_ = clock64();                 \
+    if (threadIdx.x == 0) trace[i] += now_ - tr_prev; \
+    tr_prev = now_;                                   \
+  }
+  // CTA records, one 16-byte LL pair per value: value k of CTA i at ll1 + (k * kMaxCtas + i) * 2, so that a warp
+  // reads 32 consecutive records with one fully coalesced 512-byte load.  The result record `res` (NV pairs) is the
+  // one line every other CTA polls.
+  unsigned long long* ll1 = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.ctl) + kLl1Offset);
+  unsigned long long* res = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.ctl) + kResOffset);
+  constexpr size_t kValStride = (size_t)kMaxCtas * 2;
+  bool ok = true;
+  double tot[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) tot[k] = tot_io[k];
+  if (cta != 0) {
+    // ---- level 1: release + record; level 3: wait for the result ----
+    if (lane == 0) {
+      fence_acq_rel_gpu();  // release: this CTA's stores of the phase (cumulative over the caller's barrier)
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        unsigned long long w0, w1;
+        ll_encode(tot[k], seq, w0, w1);
+        st_relaxed_gpu_v2_u64(ll1 + k * kValStride + (size_t)cta * 2, w0, w1);
+      }
+      PB_TRACE(3);  // release fence + record store
+      ok = ll_poll<NV, false>(res, 2, seq, limit, tot);
+      PB_TRACE(6);  // result poll
+      // acquire: one more look at the record, this time as an acquire load, which synchronises with CTA 0's release
+      // (fence + store) -- what every CTA released before its record is readable from here on
+      (void)ld_acquire_gpu_u64(res);
+      PB_TRACE(7);  // acquire
+    }
+  } else {
+    // ---- level 2: CTA 0 gathers the records of the rank (its own from registers; its own stores of the phase are
+    //      released by the fence in front of the result store) ----
+    {
+      // Lane l owns records l, l + 32, ...: up to kGatherUnroll of them are loaded back to back, any further ones
+      // (more than 160 CTAs per rank) one after the other.
+      double acc[NV];
+      unsigned long long t0 = 0;
+      unsigned int spins = 0;
+      while (true) {
+        bool all = true;
+        unsigned long long w[kGatherUnroll > 0 ? kGatherUnroll : 1][2 * NV];
+#pragma unroll
+        for (int j = 0; j < kGatherUnroll; ++j) {
+          const int i = lane + 32 * j;
+          if (i < ncta && i != 0) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+              ld_relaxed_gpu_v2_u64(ll1 + k * kValStride + (size_t)i * 2, w[j][2 * k], w[j][2 * k + 1]);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < NV; ++k) acc[k] = lane == 0 ? tot[k] : 0.0;  // CTA 0's own sum comes from its registers
+#pragma unroll
+        for (int j = 0; j < kGatherUnroll; ++j) {
+          const int i = lane + 32 * j;
+          if (i < ncta && i != 0) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+              all = all && ((unsigned int)(w[j][2 * k] >> 32) == seq) && ((unsigned int)(w[j][2 * k + 1] >> 32) == seq);
+              acc[k] += ll_decode(w[j][2 * k], w[j][2 * k + 1]);
+            }
+          }
+        }
+        for (int i = lane + 32 * kGatherUnroll; i < ncta; i += 32) {
+          if (i == 0) continue;
+          double v[NV];
+          all = ll_peek<NV, false>(ll1 + (size_t)i * 2, kValStride, seq, v) && all;
+#pragma unroll
+          for (int k = 0; k < NV; ++k) acc[k] += v[k];
+        }
+        if (__all_sync(0xffffffffu, all)) break;
+        if ((++spins & 0x3ffu) == 0u) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          if (__any_sync(0xffffffffu, now - t0 > limit)) {  // warp-uniform: the loop holds warp-wide votes
+            ok = false;
+            break;
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < NV; ++k) tot[k] = warp_sum_all(acc[k]);
+    }
+    PB_TRACE(4);  // gather of the CTA records
+    if (c.nranks > 1) {
+      // ---- across the ranks: one record per rank into everybody's slot area, rank-ordered sum ----
+      // (no fence: other ranks never read this rank's arrays through the reduction -- halo rows travel as
+      // self-validating records -- and the values stored here are in registers)
+      const size_t slot_off = ((size_t)(seq & 1u) * kMaxRanks) * kSlotWords;
+      if (lane < c.nranks) {  // lane rk stores this rank's record into rank rk's slot area (its own included)
+        unsigned long long* dst = c.peer_slots[lane] + slot_off + (size_t)c.rank * kSlotWords;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          unsigned long long w0, w1;
+          ll_encode(tot[k], seq, w0, w1);
+          st_relaxed_sys_v2_u64(dst + 2 * k, w0, w1);
+        }
+      }
+      double r[NV];
+#pragma unroll
+      for (int k = 0; k < NV; ++k) r[k] = 0.0;
+      if (lane < c.nranks) ok = ll_poll<NV, true>(c.slots + slot_off + (size_t)lane * kSlotWords, 2, seq, limit, r) && ok;
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        tot[k] = 0.0;
+        for (int rk = 0; rk < c.nranks; ++rk) tot[k] += __shfl_sync(0xffffffffu, r[k], rk);
+      }
+    }
+    // ---- level 3: the result record ----
+    fence_acq_rel_gpu();  // acquire the CTAs' releases and pass them on, with CTA 0's own stores, to the result record
+    ok = __all_sync(0xffffffffu, ok);
+    if (lane < NV) {
+      unsigned long long w0, w1;
+      // a gather that timed out publishes a record nobody accepts: the other CTAs then time out by themselves
+      ll_encode(lane == 0 ? tot[0] : tot[NV - 1], ok ? seq : seq ^ 0x80000000u, w0, w1);
+      st_relaxed_gpu_v2_u64(res + 2 * lane, w0, w1);
+    }
+    PB_TRACE(5);  // cross-rank part, fence, result store
+  }
+#undef PB_TRACE
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) tot_io[k] = tot[k];
+  }
+  return ok;
+}
+
+template <int NV, bool TRACE = false>
+__device__ __forceinline__ RedResult star_sum(const RankCtx& c, double (&val)[NV], unsigned int seq, int cta, int ncta,
+                                              unsigned long long limit, double* smem, long long* trace = nullptr) {
+  static_assert(NV <= kRedValues, "too many values");
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;  // nwarps <= 16
+  long long tr_prev = 0;
+  if constexpr (TRACE) tr_prev = clock64();
+#define PB_TRACE(i)                                   \
+  if constexpr (TRACE) {                              \
+    const long long now_ = clock64();                 \
+    if (threadIdx.x == 0) trace[i] += now_ - tr_prev; \
+    tr_prev = now_;                                   \
+  }
+  // ---- level 0: CTA sum ----
+  // Two values share one shuffle tree: after the first exchange the lower half-warp carries the first value, the
+  // upper half-warp the second (6 fp64 shuffle steps instead of 10; the shape is fixed, so the bits are reproducible).
+  if constexpr (NV == 2) {
+    const bool lo = lane < 16;
+    double x = (lo ? val[0] : val[1]) + __shfl_xor_sync(0xffffffffu, lo ? val[1] : val[0], 16);
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if ((lane & 15) == 0) smem[(lane >> 4) * 32 + warp] = x;
+  } else {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) val[k] += __shfl_down_sync(0xffffffffu, val[k], o);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) smem[k * 32 + warp] = val[k];
+    }
+  }
+  // Every thread orders its generic-proxy global stores of the phase before later async-proxy (TMA) reads of them;
+  // the barrier then hands them to lane 0 of warp 0, whose GPU-scope fence releases them to the other CTAs.
+  fence_proxy_async_global();
+  PB_TRACE(0);  // warp shuffles, smem write, proxy fence
+  __syncthreads();
+  PB_TRACE(1);  // barrier
+  if (warp == 0) {
+    double tot[NV];
+    if constexpr (NV == 2) {  // at most 16 warps: the half-warps reduce one value each
+      const int wl = lane & 15;
+      double x = wl < nwarps ? smem[(lane >> 4) * 32 + wl] : 0.0;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      tot[0] = __shfl_sync(0xffffffffu, x, 0), tot[1] = __shfl_sync(0xffffffffu, x, 16);
+    } else {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) tot[k] = warp_sum_all(lane < nwarps ? smem[k * 32 + lane] : 0.0);
+    }
+    PB_TRACE(2);  // lane tree over the warp sums
+    double* io = smem + 72;  // 72..73: in/out of the exchange (generic pointer into shared memory)
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) io[k] = tot[k];
+    }
+    __syncwarp();
+    const bool ok = star_exchange<NV, TRACE>(&c, io, seq, cta, ncta, limit, trace);
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) smem[64 + k] = io[k];
+      smem[64 + kRedValues] = ok ? 1.0 : 0.0;
+    }
+  }
+  __syncthreads();
+  RedResult res;
+#pragma unroll
+  for (int k = 0; k < kRedValues; ++k) res.v[k] = k < NV ? smem[64 + k] : 0.0;
+  res.ok = smem[64 + kRedValues] != 0.0;
+#undef PB_TRACE
   return res;
 }
 

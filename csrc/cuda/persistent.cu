@@ -162,7 +162,13 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
 //           the reduction whose system-scope release/acquire chain publishes them (protocol of persistent.cu)
 //   mode 2: the first CTAs store the edges, release them with one system fence each and bump the
 //           neighbour's halo counter; the reduction stays at GPU scope; CTA 0 finally checks its own
-//           counters (protocol of persistent_tma.cu)
+//           counters (the TMA kernel's first protocol, kept for comparison)
+//   mode 3: the reduction alone through star_sum (sequence-tagged records, no atomics; persistent_tma.cu)
+//   mode 4: the first CTAs store the edges as sequence-tagged LL records into the neighbours' halo lines (no fence,
+//           no counter), warp 0 of the same CTAs polls the incoming records, then star_sum: the protocol of
+//           persistent_tma.cu
+//   mode 5: mode 3 with clock64 stamps between the steps of star_sum; thread 0 of every CTA leaves the mean cycles
+//           per step in the per-CTA report area (pb_solver_cta_report)
 // CTA 0 of each rank measures the whole loop with %globaltimer -> Control::t_total (ns).
 __global__ void __launch_bounds__(kThreads, 1)
 xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters, int mode, int edge) {
@@ -177,9 +183,12 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
   }
   __syncthreads();
   unsigned int seq = c.ctl->red_seq, arrive_target = 0;
+  const unsigned int hseq = c.ctl->halo_seq;
+  const unsigned long long wd_limit = c.ctl->watchdog_ns ? c.ctl->watchdog_ns : kDefaultWatchdogNs;
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
   double check = 0.0;
   bool ok = true;
+  long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int npush = min(ncta, 16);  // mode 2: CTAs that act as "perimeter" CTAs
   unsigned long long base[4];
   for (int d = 0; d < 4; ++d) base[d] = ld_relaxed_sys_u64(c.halo_cnt + d);
@@ -217,10 +226,40 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
         if (c.nbr_r[kYp] && i < c.nx) c.nbr_r[kYp][(size_t)(i + 1) * c.nbr_pitch[kYp] + kColOff] = val;
       }
     }
+    if (mode == 4 && cta < npush && has_nbr) {
+      const unsigned int hs = hseq + (unsigned int)it + 1u;
+      const int gtid = cta * kThreads + threadIdx.x, gsz = npush * kThreads;
+      unsigned long long w0, w1;
+      ll_encode((double)(it + 1), hs, w0, w1);
+      for (int i = gtid; i < edge; i += gsz) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+          if (!c.nbr_r[d] || i >= (d < 2 ? c.ny : c.nx)) continue;
+          unsigned long long* dst = c.nbr_ll[d] + ((size_t)(hs & 1u) * (size_t)c.nbr_ll_cap[d] + (size_t)i) * 2;
+          st_relaxed_sys_u64(dst, w0);
+          st_relaxed_sys_u64(dst + 1, w1);
+        }
+      }
+      if (threadIdx.x < 32) {  // warp 0: this CTA's share of the incoming records
+        for (int d = 0; d < 4; ++d) {
+          if (!c.nbr_r[d]) continue;
+          const unsigned long long* line = c.halo_ll + ((size_t)d * 2 + (hs & 1u)) * (size_t)c.ll_cap * 2;
+          const int n = min(edge, d < 2 ? c.ny : c.nx);
+          for (int i = cta * 32 + (int)threadIdx.x; i < n; i += npush * 32) {
+            double got[1];
+            // a record that never arrives shows up in the checksum, not in the (CTA-uniform) loop condition
+            if (!ll_poll<1, true>(line + (size_t)i * 2, 2, hs, wd_limit, got) || got[0] != (double)(it + 1)) check = -1e30;
+          }
+        }
+      }
+    }
     double v[2] = {threadIdx.x == 0 ? 1.0 : 0.0, 0.0};
     ++seq;
     arrive_target += ncta;
-    const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr, mode == 1 && c.sys_scope != 0);
+    const RedResult rr = mode == 5 ? star_sum<2, true>(c, v, seq, cta, ncta, wd_limit, s_red, tr)
+                         : mode >= 3 ? star_sum<2>(c, v, seq, cta, ncta, wd_limit, s_red)
+                                   : cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr,
+                                                       mode == 1 && c.sys_scope != 0);
     ok = rr.ok;
     check += rr.v[0];
     if (mode == 2 && cta == 0 && threadIdx.x == 0) {
@@ -234,9 +273,14 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
       }
     }
   }
+  if (mode == 5 && threadIdx.x == 0) {
+    double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(c.ctl) + kCtaTimesOffset) + kCtaTimeWords * cta;
+    for (int i = 0; i < 8; ++i) mine[i] = (double)tr[i] / (double)max(1, iters);
+  }
   if (cta == 0 && threadIdx.x == 0) {
     c.ctl->t_total = globaltimer_ns() - t0;
     c.ctl->red_seq = seq;
+    c.ctl->halo_seq = hseq + (unsigned int)iters + 1u;
     c.ctl->red[0] = check;  // = iters * nranks * ncta when every reduction was complete
     c.ctl->status = ok ? PB_STATUS_CONVERGED : PB_STATUS_WATCHDOG;
   }

@@ -75,6 +75,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   __shared__ __align__(8) uint64_t s_bar[S];
   __shared__ unsigned char s_tclass[kMaxTileClass];
   __shared__ int s_filled[S];  // per stage: ring cells were unpacked for the tile in flight (thread 0 only)
+  __shared__ volatile int s_abort;  // some thread's TMA wait timed out; read after a barrier, so CTA-uniform
+  __shared__ unsigned long long s_wd_limit;  // device-side wait limit in ns (kept out of the registers)
+  __shared__ unsigned long long s_t_halo;    // thread 0: ns spent unpacking (= waiting for) the neighbours' halo records
   extern __shared__ __align__(128) unsigned char s_dyn[];
 
   const int vrank = blockIdx.x / ctas_per_rank;
@@ -90,6 +93,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       mbar_init(&s_bar[s], 1);
       s_filled[s] = 0;
     }
+    s_abort = 0;
+    s_t_halo = 0;
+    const unsigned long long wd = ctxs[vrank].ctl->watchdog_ns;
+    s_wd_limit = wd ? wd : kDefaultWatchdogNs;
     mbar_fence_init();
   }
   __syncthreads();
@@ -112,7 +119,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const bool timing = threadIdx.x == 0;  // every CTA keeps its own phase clocks; CTA 0's go into the report
   const int S_pitch = c.pitch;
 
-  unsigned int seq = ctl->red_seq, arrive_target = 0;
+  unsigned int seq = ctl->red_seq;
+#ifdef PB_VAR_OLDRED  // experiment only: the counter + aggregator reduction of the plain-load kernel
+  unsigned int arrive_target = 0;
+#define PB_RED_PRE arrive_target += ncta;
+#define PB_RED(nv) cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false)
+#else
+#define PB_RED_PRE
+#define PB_RED(nv) star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red)
+#endif
   const double delta = ctl->delta;
   const long long max_iter = ctl->max_iter;
   const int norm = ctl->norm;
@@ -176,13 +191,16 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
     const bool touch[4] = {li0 == 1, li0 + cx - 1 == c.nx, lj0 == 1, lj0 + cy - 1 == c.ny};
     const unsigned int want = hseq + (unsigned int)rounds;
-    const unsigned long long limit = ctl->watchdog_ns ? ctl->watchdog_ns : kDefaultWatchdogNs;
+    const unsigned long long limit = s_wd_limit;
     const int lane = threadIdx.x & 31;
     bool any = false;
 #pragma unroll
+    for (int d = 0; d < 4; ++d) any = any || (touch[d] && c.nbr_r[d]);
+    if (!any) return false;
+    const unsigned long long th0 = threadIdx.x == 0 ? globaltimer_ns() : 0ull;
+#pragma unroll
     for (int d = 0; d < 4; ++d) {
       if (!touch[d] || !c.nbr_r[d]) continue;
-      any = true;
       const unsigned long long* line = c.halo_ll + ((size_t)d * 2 + (want & 1u)) * (size_t)c.ll_cap * 2;
       const int t0 = d < 2 ? lj0 - 1 : li0 - 1, n = d < 2 ? cy : cx;
       for (int i = lane; i < n; i += 32) {
@@ -207,8 +225,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         c.r[(size_t)li * S_pitch + (lj + kColOff)] = v;
       }
     }
+    // every lane orders the ring cells it wrote (generic proxy) before the TMA read of the r box that lane 0 issues
+    fence_proxy_async_global();
     __syncwarp();
-    return any;
+    if (threadIdx.x == 0) s_t_halo += globaltimer_ns() - th0;
+    return true;
   };
   // Phase-AB loads of tile j into stage `st`.  part 1 = everything that does not depend on the other CTAs'
   // phase C (p and, for mixed tiles, D, a, b; arms the barrier with the full byte count), part 2 = the r box.
@@ -281,22 +302,25 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     issue_c_part(j, n_issued % S, pbuf, true, true);
     ++n_issued;
   };
+  // A stage wait that times out (an internal error: a transaction count that never completes) must not split the
+  // CTA around a barrier: the thread only raises s_abort and carries on with whatever the stage holds; every thread
+  // reads the flag after the barrier that closes the tile, so the whole CTA leaves the loop together.
   bool tma_ok = true;
   auto wait_stage = [&]() -> unsigned char* {
     const unsigned int st = n_consumed % S;
     if (!mbar_wait(&s_bar[st], (n_consumed / S) & 1u)) {
-      if (threadIdx.x == 0) {  // internal error: leave a trace and abandon; the other CTAs run into the watchdog
+      s_abort = 1;
+      if (threadIdx.x == 0) {  // leave a trace; the other CTAs run into the watchdog
         ctl->status = PB_STATUS_TMA_TIMEOUT;
         ctl->red[0] = (double)n_consumed;
         ctl->red[1] = (double)cta;
       }
-      tma_ok = false;
     }
     return stage_base + (size_t)st * Cfg::kStageBytes;
   };
-  // nothing may be in flight into shared memory when the CTA exits
+  // nothing may be in flight into shared memory when the CTA exits (no barrier inside: every thread for itself)
   auto drain = [&]() {
-    while (n_consumed < n_issued && tma_ok) {
+    while (n_consumed < n_issued && !s_abort) {
       wait_stage();
       ++n_consumed;
     }
@@ -323,8 +347,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     const int nt32 = c.tiles_x * c.tiles_y;
     for (int t = cta; t < nt32; t += ncta) v[0] += dot_zr_tile(c, t);
     ++seq;
-    arrive_target += ncta;
-    const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
+    PB_RED_PRE
+    const RedResult rr = PB_RED(1);
     if (!rr.ok) {
       drain();
       if (threadIdx.x == 0 && cta == 0) {
@@ -344,10 +368,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     double* pout = c.p[cur ^ 1];
     // ======================= phase AB (tiles 0..npre-1 are already in flight) =======================
     double acc_ab = 0.0;
-    for (int j = 0; j < nmine && tma_ok; ++j) {
+    for (int j = 0; j < nmine; ++j) {
       if (j + S - 1 < nmine) issue_ab(j + S - 1, cur, k - 1);
       unsigned char* sb = wait_stage();
-      if (!tma_ok) break;
       const double* s_r = reinterpret_cast<const double*>(sb + Cfg::kOffR);
       double* s_p = reinterpret_cast<double*>(sb + Cfg::kOffP);
       const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffD);
@@ -462,8 +485,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         run_tile(std::true_type{});
       else
         run_tile(std::false_type{});
+      // last tile: every thread orders its global stores of the phase (p_new, Ap) before the TMA reads that
+      // thread 0 issues for phase C right after the barrier
+      if (j == nmine - 1) fence_proxy_async_global();
       __syncthreads();  // stage free
       ++n_consumed;
+      if (s_abort) {
+        tma_ok = false;
+        break;
+      }
     }
     if (!tma_ok) break;
     // Prefetch for phase C: it reads only what this CTA itself wrote (p_new, Ap) or owns (w, r, D), so its
@@ -479,8 +509,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     {
       double v[1] = {acc_ab};
       ++seq;
-      arrive_target += ncta;
-      const RedResult rr = cross_rank_sum<1>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
+      PB_RED_PRE
+      const RedResult rr = PB_RED(1);
       PB_STAMP(t_r1);
       // part 2 of the prefetch: every CTA's p_new is complete and acquired (issued on every path, the barriers
       // of these stages are already armed for the bytes)
@@ -501,10 +531,9 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     alpha = zr_old / denom;
     // ======================= phase C =======================
     double acc_d = 0.0, acc_zr = 0.0;
-    for (int j = 0; j < nmine && tma_ok; ++j) {
+    for (int j = 0; j < nmine; ++j) {
       if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
       unsigned char* sb = wait_stage();
-      if (!tma_ok) break;
       const double* s_w = reinterpret_cast<const double*>(sb);
       const double* s_p = reinterpret_cast<const double*>(sb + Cfg::kTileBytes);
       const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
@@ -620,8 +649,13 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         run_tile(std::true_type{});
       else
         run_tile(std::false_type{});
+      if (j == nmine - 1) fence_proxy_async_global();  // as in phase AB: w, r before the TMA reads of the next phase
       __syncthreads();  // stage free
       ++n_consumed;
+      if (s_abort) {
+        tma_ok = false;
+        break;
+      }
     }
     if (!tma_ok) break;
     // Prefetch for the next phase AB, part 1: coefficients are constant and p_new (buffer cur^1, ring included)
@@ -639,8 +673,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     {
       double v[2] = {acc_d, acc_zr};
       ++seq;
-      arrive_target += ncta;
-      const RedResult rr = cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, false, false);
+      PB_RED_PRE
+      const RedResult rr = PB_RED(2);
       PB_STAMP(t_r2);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -666,8 +700,18 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 
   if (threadIdx.x == 0 && tma_ok) {
     // where this CTA spent the solve (ns): phase AB, phase C, waiting in reduction 1, waiting in reduction 2
-    double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(ctl) + kCtaTimesOffset) + 4 * cta;
+    double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(ctl) + kCtaTimesOffset) + kCtaTimeWords * cta;
     mine[0] = (double)t_ab, mine[1] = (double)t_c, mine[2] = (double)t_r1, mine[3] = (double)t_r2;
+    // tiles of this CTA by what they move per node and iteration (the bench's byte model counts these)
+    int n_recomp = 0, n_mixed = 0;
+    for (int j = 0; j < nmine; ++j) {
+      int li0, lj0;
+      tile_origin(j, li0, lj0);
+      n_recomp += tile_recomputes(j, li0, lj0) ? 1 : 0;
+      n_mixed += tile_mode(j) == 2 ? 1 : 0;
+    }
+    mine[4] = (double)n_recomp, mine[5] = (double)(nmine - n_mixed - n_recomp), mine[6] = (double)n_mixed;
+    mine[7] = (double)s_t_halo;
   }
   if (cta == 0 && threadIdx.x == 0 && tma_ok) {
     if (ctl->red[2] != 0.0) status = PB_STATUS_WATCHDOG;
@@ -687,8 +731,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     ctl->t_red2 = t_r2;
     ctl->t_init = t_init;
     ctl->t_total = globaltimer_ns() - t_start;
+    ctl->t_halo = s_t_halo;
   }
 #undef PB_STAMP
+#undef PB_RED
+#undef PB_RED_PRE
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -78,6 +78,10 @@ class Solver {
 
   int last_ctas_per_rank() const { return last_ctas_per_rank_; }
   long long last_launches() const { return last_launches_; }
+  int cta_report(int l, double* host_out, int max_ctas);  // the raw kCtaTimeWords doubles per CTA
+  // tiles of the last persistent TMA solve by traffic class, summed over the local ranks: constant coefficients
+  // with Ap recomputed, constant coefficients with Ap stored, mixed (coefficient boxes streamed)
+  void tile_counts(long long out[3]);
   int cta_times(int l, double* host_out, int max_ctas);  // seconds per CTA: AB, C, reduction 1, reduction 2
   bool ap_recompute(int ap_mode) const;  // resolves pb_solve_options.ap_mode (0 = by working-set size)
   size_t h2d_bytes_per_solve() const { return sizeof(DeviceOptions) * blocks_.size(); }

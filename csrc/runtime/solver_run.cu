@@ -132,14 +132,14 @@ void Solver::collect(cudaStream_t stream, pb_stats* out) {
   out->status = c0.status;
   out->diff_norm = c0.diff_norm;
   double s_in = 0, s_all = 0, mx = 0, mw = -1e300, cnt = 0;
-  unsigned long long t_ab = 0, t_c = 0, t_r1 = 0, t_r2 = 0, t_init = 0;
+  unsigned long long t_ab = 0, t_c = 0, t_r1 = 0, t_r2 = 0, t_init = 0, t_halo = 0;
   for (int l = 0; l < nlocal(); ++l) {
     const Control& c = pinned_ctl_[l];
     if (c.status == PB_STATUS_WATCHDOG) out->status = PB_STATUS_WATCHDOG;
     s_in += c.err[0], s_all += c.err[1], cnt += c.err[4];
     mx = std::max(mx, c.err[2]), mw = std::max(mw, c.err[3]);
     t_ab = std::max(t_ab, c.t_ab), t_c = std::max(t_c, c.t_c), t_r1 = std::max(t_r1, c.t_red1);
-    t_r2 = std::max(t_r2, c.t_red2), t_init = std::max(t_init, c.t_init);
+    t_r2 = std::max(t_r2, c.t_red2), t_init = std::max(t_init, c.t_init), t_halo = std::max(t_halo, c.t_halo);
   }
   out->sum_e2_in_D = s_in;
   out->sum_e2_all = s_all;
@@ -152,10 +152,15 @@ void Solver::collect(cudaStream_t stream, pb_stats* out) {
   out->t_assemble = 1e-3 * ms_asm;
   out->t_iterations = 1e-3 * ms_iter;
   if (last_method_ == kMethodPersistent || last_method_ == kMethodPersistentLdg) {
-    out->t_gpu = 1e-9 * (double)(t_ab + t_c);
+    // The reference's five buckets (S4:695-700), fed from CTA 0's device clocks; every nanosecond of the loop is in
+    // exactly one of them.  gpu = the two phases minus the halo wait inside them; comm = waiting for and unpacking
+    // the neighbours' halo records (TMA kernel; the plain-load kernel publishes its halo inside reduction 2, so its
+    // share cannot be separated and is 0 here); dot = the in-kernel reductions, cross-GPU part included; precond = 0:
+    // r/D is a few instructions inside both phases and has no time of its own; copy = 0: nothing is copied.
+    out->t_gpu = 1e-9 * (double)(t_ab + t_c - std::min(t_halo, t_ab + t_c));
     out->t_dot = 1e-9 * (double)(t_r1 + t_r2 + t_init);
-    out->t_comm = nranks() > 1 ? 1e-9 * (double)(t_r1 + t_r2) : 0.0;
-    out->t_precond = 0.25 * 1e-9 * (double)t_c;  // attributed share of phase C (one of its four streams)
+    out->t_comm = 1e-9 * (double)t_halo;
+    out->t_precond = 0.0;
     out->t_phase_ab = 1e-9 * (double)t_ab, out->t_phase_c = 1e-9 * (double)t_c;
     out->t_red1 = 1e-9 * (double)t_r1, out->t_red2 = 1e-9 * (double)t_r2;
   } else {
@@ -174,6 +179,7 @@ void Solver::xgpu_bench(int iters, int mode, int edge, int ctas, cudaStream_t st
   PB_CUDA_CHECK(cudaSetDevice(device_));
   if (ctas <= 0) ctas = sm_count_ / nlocal();
   ctas = std::min(ctas, kMaxCtas);
+  last_ctas_per_rank_ = ctas;
   for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
   PB_CUDA_CHECK(launch_xgpu_bench(dctx_, nlocal(), ctas, iters, mode, edge, stream));
   PB_CUDA_CHECK(cudaMemcpyAsync(pinned_ctl_, control(0), sizeof(Control), cudaMemcpyDeviceToHost, stream));
@@ -187,9 +193,32 @@ int Solver::cta_times(int l, double* host_out, int max_ctas) {
   PB_CUDA_CHECK(cudaSetDevice(device_));
   const int n = std::min(last_ctas_per_rank_, max_ctas);
   if (n <= 0) return 0;
-  PB_CUDA_CHECK(cudaMemcpy(host_out, arenas_[l] + kCtaTimesOffset, sizeof(double) * 4 * (size_t)n, cudaMemcpyDeviceToHost));
+  PB_CUDA_CHECK(cudaMemcpy2D(host_out, sizeof(double) * 4, arenas_[l] + kCtaTimesOffset, sizeof(double) * kCtaTimeWords,
+                             sizeof(double) * 4, (size_t)n, cudaMemcpyDeviceToHost));
   for (int i = 0; i < 4 * n; ++i) host_out[i] *= 1e-9;
   return n;
+}
+
+int Solver::cta_report(int l, double* host_out, int max_ctas) {
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  const int n = std::min(last_ctas_per_rank_, max_ctas);
+  if (n <= 0) return 0;
+  PB_CUDA_CHECK(cudaMemcpy(host_out, arenas_[l] + kCtaTimesOffset, sizeof(double) * kCtaTimeWords * (size_t)n,
+                           cudaMemcpyDeviceToHost));
+  return n;
+}
+
+void Solver::tile_counts(long long out[3]) {
+  PB_CUDA_CHECK(cudaSetDevice(device_));
+  out[0] = out[1] = out[2] = 0;
+  const int n = last_ctas_per_rank_;
+  if (n <= 0 || last_method_ != kMethodPersistent) return;
+  std::vector<double> buf((size_t)n * kCtaTimeWords);
+  for (int l = 0; l < nlocal(); ++l) {
+    PB_CUDA_CHECK(cudaMemcpy(buf.data(), arenas_[l] + kCtaTimesOffset, sizeof(double) * buf.size(), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; ++i)
+      for (int k = 0; k < 3; ++k) out[k] += (long long)buf[(size_t)i * kCtaTimeWords + 4 + k];
+  }
 }
 
 void Solver::gather_block(int l, double* dev_out, long long ld, cudaStream_t stream) {

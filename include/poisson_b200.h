@@ -145,6 +145,14 @@ int pb_solver_info(pb_solver* s, int* ctas_per_rank, long long* launches, long l
 /* Per-CTA device clocks of the last persistent (TMA) solve: out[4 * cta + {0,1,2,3}] = seconds in phase AB, phase C,
    waiting in reduction 1, waiting in reduction 2.  Returns the number of CTAs written (<= max_ctas) or < 0. */
 int pb_solver_cta_times(pb_solver* s, int local_idx, double* host_out, int max_ctas);
+/* The raw per-CTA report area: 8 doubles per CTA (after a solve: ns in AB, C, reduction 1, reduction 2, the three tile
+   counts below, ns waiting for halo records; after pb_solver_xgpu_bench mode 5: mean clock cycles per step of the
+   reduction).  Returns the number of CTAs written or < 0. */
+int pb_solver_cta_report(pb_solver* s, int local_idx, double* host_out, int max_ctas);
+/* Tiles of the last persistent (TMA) solve by what they move per node and iteration, summed over the local ranks:
+   out3 = {constant coefficients with Ap recomputed (64 B), constant coefficients with Ap stored (80 B), mixed tiles
+   that stream a, b, D (112 B)}.  Counted by the kernel itself; the benchmark's roofline uses these. */
+int pb_solver_tile_counts(pb_solver* s, long long* out3);
 /* 1 if a solve with this ap_mode recomputes Ap in phase C on this solver's blocks (0 resolves by working-set size) */
 int pb_solver_ap_recompute(pb_solver* s, int ap_mode);
 
@@ -192,7 +200,9 @@ int pb_apply_A_dot_noalloc(int M, int N, int nx, int ny, int pitch, const void* 
                            void* Ap, void* dot_out, void* cuda_stream);
 
 /* communication micro-benchmark (collective over all ranks): `iters` rounds of the in-kernel cross-rank
- * reduction (mode 0) or of halo stores of `edge` doubles per neighbour + reduction (mode 1);
+ * reduction (mode 0: counter + elected aggregator, the plain-load kernel's; mode 3: the record star of the TMA
+ * kernel; mode 5: mode 3 with per-step clocks) or of halo stores of `edge` doubles per neighbour + reduction
+ * (modes 1, 2: fenced stores; mode 4: halo rows as sequence-tagged records + record star, the TMA kernel's protocol);
  * out2 = {ns per round measured on this rank, checksum}.  ctas = 0: one CTA per SM. */
 int pb_solver_xgpu_bench(pb_solver* s, int iters, int mode, int edge, int ctas, void* cuda_stream, double* out2);
 /* unit test: compares x*y, one- and two-correction Markstein quotients with x / h on n pseudo-random x;

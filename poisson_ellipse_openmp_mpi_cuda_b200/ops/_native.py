@@ -127,6 +127,8 @@ def _declare(lib: C.CDLL) -> None:
         "pb_solver_info": (I, [vp, C.POINTER(I), C.POINTER(LL), C.POINTER(LL), C.POINTER(LL)]),
         "pb_solver_ap_recompute": (I, [vp, I]),
         "pb_solver_cta_times": (I, [vp, I, dp, I]),
+        "pb_solver_cta_report": (I, [vp, I, dp, I]),
+        "pb_solver_tile_counts": (I, [vp, C.POINTER(LL)]),
         "pb_group_create": (vp, [I, I, I, I, C.POINTER(I), I]),
         "pb_group_destroy": (None, [vp]),
         "pb_group_solve": (I, [vp, C.POINTER(SolveOptions), C.POINTER(Stats)]),
@@ -151,7 +153,9 @@ def _declare(lib: C.CDLL) -> None:
         "pb_step_read_control": (I, [vp, I, C.POINTER(I), C.POINTER(I), C.POINTER(D), vp]),
     })
     for name, (res, args) in sig.items():
-        fn = getattr(lib, name)
+        fn = getattr(lib, name, None)
+        if fn is None:  # an older library selected through POISSON_B200_LIB (A/B runs): the call itself will fail
+            continue
         fn.restype = res
         fn.argtypes = args
 

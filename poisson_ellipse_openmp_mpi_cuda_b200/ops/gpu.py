@@ -136,6 +136,20 @@ class GpuSolver:
         _native.check(min(got, 0), "pb_solver_cta_times")
         return out[:max(got, 0)]
 
+    def cta_report(self, local_idx: int = 0) -> torch.Tensor:
+        """Raw per-CTA report words ``[ctas, 8]`` (see ``pb_solver_cta_report``)."""
+        n = self.info()["ctas_per_rank"]
+        out = torch.zeros((max(n, 1), 8), dtype=torch.float64)
+        got = self.lib.pb_solver_cta_report(self._h, local_idx, C.cast(out.data_ptr(), C.POINTER(C.c_double)), n)
+        _native.check(min(got, 0), "pb_solver_cta_report")
+        return out[:max(got, 0)]
+
+    def tile_counts(self) -> dict:
+        """Tiles of the last persistent (TMA) solve by bytes moved per node and iteration (counted by the kernel)."""
+        out = (C.c_longlong * 3)()
+        _native.check(self.lib.pb_solver_tile_counts(self._h, out), "pb_solver_tile_counts")
+        return {"recompute_64B": out[0], "stored_80B": out[1], "mixed_112B": out[2]}
+
     def recomputes_ap(self, ap_mode: int = 0) -> bool:
         """Whether a solve with this ``ap_mode`` recomputes Ap in phase C (0 = decided by working-set size vs L2)."""
         return bool(self.lib.pb_solver_ap_recompute(self._h, int(ap_mode)))
