@@ -39,7 +39,11 @@ def main():
     rows = []
     fs.solver.xgpu_bench(50, 0, 0)  # warm-up
     ns, chk = fs.solver.xgpu_bench(iters, 0, 0)
-    rows.append({"what": "allreduce_2xf64", "impl": "ours_in_kernel", "us": max_over_ranks(ns, dev) / 1e3,
+    rows.append({"what": "allreduce_2xf64", "impl": "ours_counter+aggregator (plain-load kernel)",
+                 "us": max_over_ranks(ns, dev) / 1e3, "checksum_ok": chk == iters * world * 148})
+    fs.solver.xgpu_bench(50, 3, 0)
+    ns, chk = fs.solver.xgpu_bench(iters, 3, 0)
+    rows.append({"what": "allreduce_2xf64", "impl": "ours_record_star (TMA kernel)", "us": max_over_ranks(ns, dev) / 1e3,
                  "checksum_ok": chk == iters * world * 148})
     nbrs = [n for n in blk.nbr if n >= 0]
     for edge in (64, 256, 1024, 4096, 16384):
@@ -51,6 +55,11 @@ def main():
         ns, _ = fs.solver.xgpu_bench(iters, 2, edge)
         rows.append({"what": "halo_exchange", "edge_doubles": edge, "impl": "ours_peer_store+counter+reduction",
                      "us": max_over_ranks(ns, dev) / 1e3, "neighbours": len(nbrs)})
+        fs.solver.xgpu_bench(20, 4, edge)
+        ns, chk = fs.solver.xgpu_bench(iters, 4, edge)
+        rows.append({"what": "halo_exchange", "edge_doubles": edge, "impl": "ours_ll_records+record_star (TMA kernel)",
+                     "us": max_over_ranks(ns, dev) / 1e3, "neighbours": len(nbrs),
+                     "checksum_ok": chk == iters * world * 148})
     if world > 1:
         x = torch.ones(2, dtype=torch.float64, device=dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

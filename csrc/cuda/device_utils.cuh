@@ -241,9 +241,9 @@ __device__ __forceinline__ RedResult cross_rank_sum(const RankCtx& c, double (&v
 //   level 0  CTA sum: lane tree per warp -> shared memory -> one __syncthreads -> lane tree over the warp sums
 //   level 1  lane 0 releases the CTA's global stores with one GPU-scope fence and writes an LL record (each 8-byte
 //            word = 32 bits of payload | sequence number, so the record carries its own validity) into ll1[k][cta]
-//   level 2  warp 0 of CTA 0 looks at all records of the rank at once (lane l reads records l, l+32, ... back to
-//            back, every load of a look in flight together, so the fan-in costs one hop, not one per record) and
-//            adds them in a fixed order.  Several ranks: it stores the rank's record into every rank's slot area
+//   level 2  warp 0 of CTA 0 looks at all records of the rank at once (lane l copies records l, l+32, ... into shared
+//            memory with cp.async, every copy of a look in flight together, so the fan-in costs one hop, not one per
+//            record, and no registers) and adds them in a fixed order.  Several ranks: it stores the rank's record into every rank's slot area
 //            over NVLink, polls its own slot area and adds the ranks' records in rank order.
 //   level 3  the same warp fences and stores the result record; lane 0 of warp 0 of every other CTA polls it (147
 //            such pollers on one line cost nothing measurable; private mailboxes written by CTA 0 were not faster),
@@ -322,24 +322,33 @@ __device__ __forceinline__ double warp_sum_all(double x) {
   return x;
 }
 
-#ifdef PB_VAR_INLINE  // experiment only
-#define PB_EXCHANGE_INLINE __forceinline__
-#else
+#ifdef PB_VAR_NOINLINE  // experiment only
 #define PB_EXCHANGE_INLINE __noinline__
-#endif
-#ifdef PB_VAR_NOUNROLL  // experiment only
-constexpr int kGatherUnroll = 0;
 #else
-constexpr int kGatherUnroll = 5;
+#define PB_EXCHANGE_INLINE __forceinline__
 #endif
 
+// Staging area of CTA 0's gather: the records travel global -> shared memory with cp.async (L2 only, no register
+// per load in flight), kGatherSlots records per value.  One instance per kernel.
+constexpr int kGatherSlots = 160;
+__device__ __forceinline__ unsigned long long* star_gather_buf() {
+  __shared__ __align__(16) unsigned long long buf[kRedValues * kGatherSlots * 2];
+  return buf;
+}
+__device__ __forceinline__ void cp_async_cg_16(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned int)__cvta_generic_to_shared(smem_dst)),
+               "l"(gmem_src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // Levels 1-3 of star_sum, executed by warp 0 of every CTA: tot_io holds the CTA's sums on entry and the global sums
-// on return.  Not inlined on purpose: the gather keeps up to 20 loads in flight and must not cost the tile loops of
-// the calling kernel any registers.
+// on return.  The gather must not cost the tile loops of the calling kernel any registers (a version that kept its 20
+// loads of a look in registers made ptxas spill in the tile loops, inlined or not: phases +10 %), hence cp.async.
 // TRACE (micro-benchmark only): thread 0 adds the clock64 distance between the numbered steps to trace[3..7].
 template <int NV, bool TRACE>
-__device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_io, unsigned int seq, int cta, int ncta,
-                                                 unsigned long long limit, long long* trace) {
+__device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_io, unsigned long long* gbuf, unsigned int seq,
+                                                 int cta, int ncta, unsigned long long limit, long long* trace) {
   const RankCtx& c = *cp;
   const int lane = threadIdx.x & 31;
   long long tr_prev = 0;
@@ -382,38 +391,31 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
     // ---- level 2: CTA 0 gathers the records of the rank (its own from registers; its own stores of the phase are
     //      released by the fence in front of the result store) ----
     {
-      // Lane l owns records l, l + 32, ...: up to kGatherUnroll of them are loaded back to back, any further ones
-      // (more than 160 CTAs per rank) one after the other.
+      // Lane l owns records l, l + 32, ...: the first kGatherSlots records of every value are copied to shared memory
+      // with cp.async, all copies of a look in flight together, and checked there; any further ones (more than 160
+      // CTAs per rank) are looked at one after the other.
       double acc[NV];
       unsigned long long t0 = 0;
       unsigned int spins = 0;
+      const int nfast = min(ncta, kGatherSlots);
       while (true) {
         bool all = true;
-        unsigned long long w[kGatherUnroll > 0 ? kGatherUnroll : 1][2 * NV];
+        for (int i = lane == 0 ? 32 : lane; i < nfast; i += 32) {
 #pragma unroll
-        for (int j = 0; j < kGatherUnroll; ++j) {
-          const int i = lane + 32 * j;
-          if (i < ncta && i != 0) {
-#pragma unroll
-            for (int k = 0; k < NV; ++k)
-              ld_relaxed_gpu_v2_u64(ll1 + k * kValStride + (size_t)i * 2, w[j][2 * k], w[j][2 * k + 1]);
-          }
+          for (int k = 0; k < NV; ++k) cp_async_cg_16(gbuf + ((size_t)k * kGatherSlots + i) * 2, ll1 + k * kValStride + (size_t)i * 2);
         }
+        cp_async_wait_all();  // every lane reads back only what it copied itself
 #pragma unroll
         for (int k = 0; k < NV; ++k) acc[k] = lane == 0 ? tot[k] : 0.0;  // CTA 0's own sum comes from its registers
+        for (int i = lane == 0 ? 32 : lane; i < nfast; i += 32) {
 #pragma unroll
-        for (int j = 0; j < kGatherUnroll; ++j) {
-          const int i = lane + 32 * j;
-          if (i < ncta && i != 0) {
-#pragma unroll
-            for (int k = 0; k < NV; ++k) {
-              all = all && ((unsigned int)(w[j][2 * k] >> 32) == seq) && ((unsigned int)(w[j][2 * k + 1] >> 32) == seq);
-              acc[k] += ll_decode(w[j][2 * k], w[j][2 * k + 1]);
-            }
+          for (int k = 0; k < NV; ++k) {
+            const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(gbuf + ((size_t)k * kGatherSlots + i) * 2);
+            all = all && ((unsigned int)(w.x >> 32) == seq) && ((unsigned int)(w.y >> 32) == seq);
+            acc[k] += ll_decode(w.x, w.y);
           }
         }
-        for (int i = lane + 32 * kGatherUnroll; i < ncta; i += 32) {
-          if (i == 0) continue;
+        for (int i = lane + kGatherSlots; i < ncta; i += 32) {
           double v[NV];
           all = ll_peek<NV, false>(ll1 + (size_t)i * 2, kValStride, seq, v) && all;
 #pragma unroll
@@ -534,7 +536,7 @@ __device__ __forceinline__ RedResult star_sum(const RankCtx& c, double (&val)[NV
       for (int k = 0; k < NV; ++k) io[k] = tot[k];
     }
     __syncwarp();
-    const bool ok = star_exchange<NV, TRACE>(&c, io, seq, cta, ncta, limit, trace);
+    const bool ok = star_exchange<NV, TRACE>(&c, io, star_gather_buf(), seq, cta, ncta, limit, trace);
     if (lane == 0) {
 #pragma unroll
       for (int k = 0; k < NV; ++k) smem[64 + k] = io[k];

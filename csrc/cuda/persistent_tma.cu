@@ -303,12 +303,14 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     ++n_issued;
   };
   // A stage wait that times out (an internal error: a transaction count that never completes) must not split the
-  // CTA around a barrier: the thread only raises s_abort and carries on with whatever the stage holds; every thread
-  // reads the flag after the barrier that closes the tile, so the whole CTA leaves the loop together.
-  bool tma_ok = true;
+  // CTA around a barrier: the thread only raises s_abort, stops waiting for further stages (`waiting`, per thread)
+  // and carries on with whatever the stages hold; every thread reads the flag once after the last barrier of the
+  // phase, so the whole CTA leaves the iteration together.
+  bool tma_ok = true, waiting = true;
   auto wait_stage = [&]() -> unsigned char* {
     const unsigned int st = n_consumed % S;
-    if (!mbar_wait(&s_bar[st], (n_consumed / S) & 1u)) {
+    if (waiting && !mbar_wait(&s_bar[st], (n_consumed / S) & 1u)) {
+      waiting = false;
       s_abort = 1;
       if (threadIdx.x == 0) {  // leave a trace; the other CTAs run into the watchdog
         ctl->status = PB_STATUS_TMA_TIMEOUT;
@@ -490,12 +492,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (j == nmine - 1) fence_proxy_async_global();
       __syncthreads();  // stage free
       ++n_consumed;
-      if (s_abort) {
-        tma_ok = false;
-        break;
-      }
     }
-    if (!tma_ok) break;
+    if (s_abort) {
+      tma_ok = false;
+      break;
+    }
     // Prefetch for phase C: it reads only what this CTA itself wrote (p_new, Ap) or owns (w, r, D), so its
     // first tiles can be in flight while the reduction below waits for the slowest CTA / GPU.  The exception is
     // the p_new box with ring of a tile that recomputes Ap (part 2, issued right after the reduction).
@@ -652,12 +653,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (j == nmine - 1) fence_proxy_async_global();  // as in phase AB: w, r before the TMA reads of the next phase
       __syncthreads();  // stage free
       ++n_consumed;
-      if (s_abort) {
-        tma_ok = false;
-        break;
-      }
     }
-    if (!tma_ok) break;
+    if (s_abort) {
+      tma_ok = false;
+      break;
+    }
     // Prefetch for the next phase AB, part 1: coefficients are constant and p_new (buffer cur^1, ring included)
     // was completed before the previous reduction.  The r box waits for the reduction below, because its
     // ring cells are written by other CTAs / GPUs during this very phase.
