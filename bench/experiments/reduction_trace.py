@@ -28,7 +28,7 @@ def main():
     print(json.dumps({"mode": 5, "what": "record star, traced", "us_per_reduction": ns / 1e3,
                       "cycles_cta0": dict(zip(STEPS, [round(float(v)) for v in rep[0]])),
                       "cycles_others_mean": dict(zip(STEPS, [round(float(v)) for v in rep[1:].mean(dim=0)])),
-                      "cycles_others_max": dict(zip(STEPS, [round(float(v)) for v in rep[1:].max(dim=0).values])))})
+                      "cycles_others_max": dict(zip(STEPS, [round(float(v)) for v in rep[1:].max(dim=0).values]))}))
     s.close()
 
 
