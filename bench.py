@@ -90,6 +90,65 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
+def measured_hbm_gbs() -> tuple[float, str]:
+    """Copy bandwidth of this pool's B200 from the driver-written MEASURED_PEAKS.json (else the profiling recipe's
+    fallback, and say so)."""
+    try:
+        return float(json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# In-kernel all-reduce of two doubles, one reduction, microseconds by GPU count (bench/halo_allreduce_sweep.py, record
+# star; profiles/halo_allreduce_sweep_*gpu.jsonl).  The floor of an iteration is two of them.
+REDUCTION_FLOOR_US = {1: 3.3, 2: 5.0, 4: 5.5, 8: 6.0}
+NVLINK_GBS_PER_DIRECTION = 900.0
+
+
+def roofline(M: int, N: int, world: int, grid, tiles: dict, us_iter: float, l2_bytes: int = 126 << 20) -> dict:
+    """The north-star roofline of one iteration on the busiest GPU: max(HBM bytes at the copy bandwidth, halo bytes
+    over NVLink) + the latency floor of the two reductions.  Bytes are counted from the kernel's own tile classes
+    (64 / 80 / 112 B per node and iteration), not assumed."""
+    nodes = (M - 1) * (N - 1)
+    nt = max(1, sum(tiles.values()))
+    bytes_node = (64.0 * tiles["recompute_64B"] + 80.0 * tiles["stored_80B"] + 112.0 * tiles["mixed_112B"]) / nt
+    bytes_iter = bytes_node * nodes / world
+    hbm_gbs, src = measured_hbm_gbs()
+    px, py = grid
+    # halo: every shared edge node travels as one 16-byte record per iteration, both directions at once
+    edge_nodes = (min(2, px - 1) * ((N - 1) // py + 1) if px > 1 else 0) + (min(2, py - 1) * ((M - 1) // px + 1) if py > 1 else 0)
+    nvlink_s = edge_nodes * 16.0 / (NVLINK_GBS_PER_DIRECTION * 1e9)
+    hbm_s, hbm_s_nominal = bytes_iter / (hbm_gbs * 1e9), bytes_iter / 8e12
+    red_s = 2e-6 * REDUCTION_FLOOR_US.get(world, REDUCTION_FLOOR_US[8])
+    model_s = max(hbm_s, nvlink_s) + red_s
+    working_set = 5 * 8 * nodes / world
+    return {"bytes_per_node_iter": bytes_node, "tiles": tiles, "bytes_per_iter_per_gpu": bytes_iter,
+            "hbm_gbs_used_for_roofline": hbm_gbs, "hbm_gbs_source": src,
+            "hbm_us": 1e6 * hbm_s, "hbm_us_at_8TBs": 1e6 * hbm_s_nominal, "nvlink_us": 1e6 * nvlink_s,
+            "reduction_floor_us": 1e6 * red_s, "model_us": 1e6 * model_s, "measured_us": us_iter,
+            "fraction_of_roofline": model_s / (us_iter * 1e-6) if us_iter > 0 else None,
+            "fraction_of_hbm_bandwidth": hbm_s / (us_iter * 1e-6) if us_iter > 0 else None,
+            "l2_resident": working_set < 0.8 * l2_bytes,
+            "note": "an L2-resident block (w, r, p, p', Ap of one GPU < 80 % of L2) is not bound by HBM: its fraction "
+                    "says how close the iteration is to what HBM would allow, not to a roof it could hit"}
+
+
+def cli_cold_seconds(M: int, N: int, gpus: int) -> dict | None:
+    """Process wall time and printed lines of the product's CLI -- the reference's only interface -- from a cold
+    start: `poisson_b200 M N --gpus G` (one process drives all G GPUs)."""
+    exe = ROOT / "poisson_ellipse_openmp_mpi_cuda_b200" / "bin" / "poisson_b200"
+    if not exe.exists():
+        return None
+    t0 = time.perf_counter()
+    p = subprocess.run([str(exe), str(M), str(N), "--gpus", str(gpus)], capture_output=True, text=True)
+    wall = time.perf_counter() - t0
+    if p.returncode != 0:
+        return {"error": p.stderr[-200:], "process_wall_s": wall}
+    return {"process_wall_s": wall, "printed_total_time_s": _grab(r"Total Time=([0-9.eE+-]+) s", p.stdout),
+            "printed_solver_time_s": _grab(r"Solver time \(MPI\+CUDA\)\s+~ ([0-9.eE+-]+)", p.stdout),
+            "printed_init_time_s": _grab(r"Init time \(program\)\s+~ ([0-9.eE+-]+)", p.stdout)}
+
+
 def _env():
     return (int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0)))
 
@@ -153,11 +212,18 @@ def run_ours(a) -> dict:
     gpu_solver = solver._impl.solver if world > 1 else solver._impl
     info = gpu_solver.info()
     recomputes = gpu_solver.recomputes_ap(a.ap_mode)
-    bytes_node = 64.0 if recomputes else 80.0
+    # tile classes counted by the kernel, summed over the ranks -> bytes actually moved per node and iteration
+    tc = gpu_solver.tile_counts()
+    tct = torch.tensor([tc["recompute_64B"], tc["stored_80B"], tc["mixed_112B"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tct)
+    tiles = dict(zip(("recompute_64B", "stored_80B", "mixed_112B"), (int(v) for v in tct.tolist())))
     value = sum(dev_s) / len(dev_s)
     e2e = sum(e2e_s) / len(e2e_s)
     us_iter = 1e6 * res["t_iterations"] / max(1, res["iters"])
     nodes = (M - 1) * (N - 1)
+    roof = roofline(M, N, world, solver.grid, tiles, us_iter)
+    bytes_node = roof["bytes_per_node_iter"]
     out = {
         "metric": f"pcg_time_to_converge_{M}x{N}", "value": value, "unit": "s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * value, "higher_is_better": False, "scaling": "strong",
@@ -178,11 +244,15 @@ def run_ours(a) -> dict:
         "e2e": {"value": e2e, "unit": "s", "samples": e2e_s, "h2d_bytes_per_step": info["h2d_bytes"], "d2h_bytes_per_step": info["d2h_bytes"],
                 "what": "poisson_b200.solve(M, N): options pinned->device, assembly, PCG, error report, result "
                         "block device->pinned; wall clock, max over ranks"},
-        "gpu_launches": launches, "clocks": clocks,
+        "gpu_launches": launches, "clocks": clocks, "roofline": roof,
         "timers_s": {k: res[k] for k in ("t_assemble", "t_iterations", "t_gpu", "t_comm", "t_dot", "t_phase_ab", "t_phase_c",
                                            "t_red1", "t_red2")},
     }
     pb.clear_cache()
+    if world > 1:
+        dist.barrier()
+    if rank == 0 and a.cli_cold:
+        out["cli_cold"] = cli_cold_seconds(M, N, world)  # after the timed regions; the other ranks idle meanwhile
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -327,6 +397,8 @@ def main():
                     help="stencil divisions by h1/h2: markstein = correctly rounded 3-instruction sequence (same "
                          "bits as 'true'), true = IEEE division, recip = multiply by the reciprocal")
     ap.add_argument("--tile-rows", type=int, default=0)
+    ap.add_argument("--no-cli-cold", dest="cli_cold", action="store_false",
+                    help="skip the extra cold run of the CLI (reported as `cli_cold`, outside every timed region)")
     ap.add_argument("--ap-mode", type=int, default=0, choices=[0, 1, 2],
                     help="constant-coefficient tiles: 1 store and reload Ap, 2 recompute it in phase C, 0 library default")
     a = ap.parse_args()

@@ -56,6 +56,18 @@ void pb_choose_proc_grid(int nranks, int* Px, int* Py) {
   *Py = g.Py;
 }
 
+int pb_choose_grid_topology(int n, const int* perf, int M, int* Px, int* Py, int* order) {
+  if (n < 1 || n > 64 || !perf || !Px || !Py || !order) {
+    pb::set_last_error("pb_choose_grid_topology: 1..64 devices and non-null arguments are required");
+    return -1;
+  }
+  pb::ProcGrid g;
+  const int kind = pb::choose_grid_from_topology(n, perf, M, 32, &g, order);
+  *Px = g.Px;
+  *Py = g.Py;
+  return kind;
+}
+
 int pb_local_block(int M, int N, int Px, int Py, int rank, pb_block* out) {
   if (M < 2 || N < 2 || Px < 1 || Py < 1 || rank < 0 || rank >= Px * Py) {
     pb::set_last_error("pb_local_block: invalid arguments");

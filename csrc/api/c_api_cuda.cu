@@ -145,6 +145,13 @@ int pb_solver_tile_counts(pb_solver* s, long long* out3) {
 int pb_solver_ap_recompute(pb_solver* s, int ap_mode) { return s->impl.ap_recompute(ap_mode) ? 1 : 0; }
 
 // ---- single-process multi-GPU group ----
+int pb_runtime_bootstrap(const int* devices, int n) {
+  return guarded([&] { pb::bootstrap_devices(std::vector<int>(devices, devices + n)); });
+}
+int pb_p2p_matrix(const int* devices, int n, int* perf, int* access, int* atomics) {
+  return guarded([&] { pb::p2p_matrix(std::vector<int>(devices, devices + n), perf, access, atomics); });
+}
+
 pb_group* pb_group_create(int M, int N, int Px, int Py, const int* devices, int ndevices) {
   try {
     return new pb_group(M, N, Px, Py, std::vector<int>(devices, devices + ndevices));

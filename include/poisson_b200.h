@@ -66,6 +66,11 @@ const char* pb_last_error(void);
 
 /* ---- decomposition (replaces choose_process_grid S4:82-86 and decompose_2d S4:97-133) ---- */
 void pb_choose_proc_grid(int nranks, int* Px, int* Py);
+/* Process grid and device order from a peer-to-peer performance matrix (perf[a*n+b], lower = better; see
+ * csrc/core/decomp.h): uniform fabric -> n x 1 slabs, equal islands -> islands x members with the x-cuts between the
+ * islands, else the reference's grid.  order[rank] = index of the device that runs `rank`.  Returns 0 / 1 / 2 for
+ * these three cases, < 0 on bad arguments. */
+int pb_choose_grid_topology(int n, const int* perf, int M, int* Px, int* Py, int* order);
 int pb_local_block(int M, int N, int Px, int Py, int rank, pb_block* out);
 int pb_col_offset(void); /* column of ring cell lj=0 inside a padded row */
 
@@ -126,6 +131,13 @@ typedef struct pb_solve_options {
 } pb_solve_options;
 
 int pb_cuda_device_count(void);
+/* Runtime bootstrap for `n` devices, the counterpart of the reference's MPI_Init + launcher GPU binding (S4:986-990,
+ * SURVEY.md section 0.7): creates the primary contexts and enables peer access between every pair, one host thread
+ * per device.  Idempotent; pb_group_create calls it itself. */
+int pb_runtime_bootstrap(const int* devices, int n);
+/* Peer-to-peer topology of `n` devices as CUDA reports it: perf[a*n+b] = cudaDevP2PAttrPerformanceRank of a -> b
+ * (lower is better), access / atomics = cudaDevP2PAttrAccessSupported / NativeAtomicSupported; diagonals are 0 / 1 / 1. */
+int pb_p2p_matrix(const int* devices, int n, int* perf, int* access, int* atomics);
 pb_solver* pb_solver_create(int M, int N, int Px, int Py, int first_rank, int nlocal, int device);
 void pb_solver_destroy(pb_solver* s);
 int pb_solver_ipc_handle(pb_solver* s, int local_idx, void* out64);

@@ -56,8 +56,15 @@ class PoissonSolver:
             from .parallel.decomp import parse_grid as _pg
 
             n = torch.cuda.device_count() if gpus is None else int(gpus)
-            self.grid = _pg("auto" if grid is None else grid, n, M)
-            self._impl = GroupSolver(M, N, self.grid[0], self.grid[1])
+            devices = None
+            if grid is None or grid == "auto":
+                from .parallel.topology import grid_from_topology, probe_p2p
+
+                px, py, devices, _ = grid_from_topology(probe_p2p(range(n))["perf"], M)
+                self.grid = (px, py)
+            else:
+                self.grid = _pg(grid, n, M)
+            self._impl = GroupSolver(M, N, self.grid[0], self.grid[1], devices)
         elif backend == "virtual":
             from .ops.gpu import GpuSolver
 

@@ -89,6 +89,8 @@ def _declare(lib: C.CDLL) -> None:
         "pb_version": (C.c_int, []),
         "pb_last_error": (C.c_char_p, []),
         "pb_choose_proc_grid": (None, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+        "pb_choose_grid_topology": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int),
+                                              C.POINTER(C.c_int), C.POINTER(C.c_int)]),
         "pb_local_block": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Block)]),
         "pb_col_offset": (C.c_int, []),
         "pb_coef_a": (C.c_double, [C.c_int] * 4),
@@ -110,6 +112,8 @@ def _declare(lib: C.CDLL) -> None:
     I, LL, D = C.c_int, C.c_longlong, C.c_double
     sig.update({
         "pb_cuda_device_count": (I, []),
+        "pb_runtime_bootstrap": (I, [C.POINTER(I), I]),
+        "pb_p2p_matrix": (I, [C.POINTER(I), I, C.POINTER(I), C.POINTER(I), C.POINTER(I)]),
         "pb_solver_create": (vp, [I] * 7),
         "pb_solver_destroy": (None, [vp]),
         "pb_solver_ipc_handle": (I, [vp, I, vp]),

@@ -49,16 +49,44 @@ class FusedMultiGpuSolver:
 
     def __init__(self, M: int, N: int, grid="auto", device: int | None = None):
         self.rank, self.world = world_info()
-        self.Px, self.Py = parse_grid("auto" if grid is None else grid, self.world, M)
         self.M, self.N = M, N
         self.device = torch.cuda.current_device() if device is None else device
-        self.solver = GpuSolver(M, N, self.Px, self.Py, first_rank=self.rank, nlocal=1, device=self.device)
+        self.topology = None
+        # which block of the Px x Py grid this process owns; the identity unless the topology says otherwise
+        self.block_id = self.rank
+        if self.world > 1:
+            # single-node scope: the data plane is CUDA IPC + peer access (the reference's MPI stage also runs
+            # across nodes; this backend does not -- use backend="nccl" there)
+            import socket
+
+            hosts = [None] * self.world
+            dist.all_gather_object(hosts, (socket.gethostname(), self.device))
+            if len({h for h, _ in hosts}) > 1:
+                raise RuntimeError("backend='fused' connects the ranks through CUDA IPC and peer access and therefore "
+                                   f"needs all ranks on one node (found hosts {sorted({h for h, _ in hosts})}); "
+                                   "use backend='nccl' across nodes")
+            devices = [d for _, d in hosts]
+        if self.world > 1 and (grid is None or grid == "auto"):
+            # grid and block placement from the peer-to-peer topology of the ranks' devices (every rank computes the
+            # same answer from the same matrix)
+            from .topology import grid_from_topology, probe_p2p
+
+            try:
+                perf = probe_p2p(devices)["perf"]
+                self.Px, self.Py, order, kind = grid_from_topology(perf, M)
+                self.block_id = order.index(self.rank)
+                self.topology = {"kind": kind, "perf": perf, "order": order}
+            except Exception:  # noqa: BLE001 -- no probe possible (e.g. devices hidden from this process)
+                self.Px, self.Py = parse_grid("auto", self.world, M)
+        else:
+            self.Px, self.Py = parse_grid("auto" if grid is None else grid, self.world, M)
+        self.solver = GpuSolver(M, N, self.Px, self.Py, first_rank=self.block_id, nlocal=1, device=self.device)
         if self.world > 1:
             handles = [None] * self.world
-            dist.all_gather_object(handles, self.solver.ipc_handle(0))
-            for rk, h in enumerate(handles):
+            dist.all_gather_object(handles, (self.block_id, self.solver.ipc_handle(0)))
+            for rk, (blk, h) in enumerate(handles):
                 if rk != self.rank:
-                    self.solver.open_peer(rk, h)
+                    self.solver.open_peer(blk, h)
         self.solver.finalize()
         if self.world > 1:
             dist.barrier()  # every arena is mapped everywhere before the first kernel stores into a peer

@@ -84,3 +84,15 @@ def test_reference_arm_end_to_end_with_a_stand_in_program(tmp_path):
     for k in REQUIRED:
         assert k in line, k
     assert line["value"] == 4.762518 and line["e2e"]["value"] == 4.7626 and len(line["samples"]) == 2
+
+
+def test_roofline_block_counts_bytes_from_tile_classes():
+    tiles = {"recompute_64B": 90, "stored_80B": 0, "mixed_112B": 10}
+    r = bench.roofline(4096, 4096, 1, (1, 1), tiles, us_iter=230.0)
+    assert math.isclose(r["bytes_per_node_iter"], 0.9 * 64 + 0.1 * 112)
+    assert r["nvlink_us"] == 0.0 and not r["l2_resident"]
+    assert math.isclose(r["model_us"], r["hbm_us"] + r["reduction_floor_us"])
+    assert 0.0 < r["fraction_of_roofline"] < 1.5 and r["fraction_of_hbm_bandwidth"] < r["fraction_of_roofline"]
+    r8 = bench.roofline(4096, 4096, 8, (8, 1), {"recompute_64B": 0, "stored_80B": 100, "mixed_112B": 0}, us_iter=36.0)
+    assert r8["l2_resident"] and r8["nvlink_us"] > 0 and math.isclose(r8["bytes_per_node_iter"], 80.0)
+    assert math.isclose(r8["bytes_per_iter_per_gpu"], 80.0 * 4095 * 4095 / 8)
