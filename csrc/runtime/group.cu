@@ -11,6 +11,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <exception>
 #include <thread>
 
@@ -78,11 +81,24 @@ void p2p_matrix(const std::vector<int>& devices, int* perf, int* access, int* at
     }
 }
 
+// PB_TRACE_INIT=1: where a cold start spends its time, on stderr
+static double trace_now() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+static void trace_init(const char* what, double& t_prev) {
+  static const bool on = std::getenv("PB_TRACE_INIT") != nullptr;
+  const double t = trace_now();
+  if (on) std::fprintf(stderr, "[pb init] %-28s %.3f s\n", what, t - t_prev);
+  t_prev = t;
+}
+
 DeviceGroup::DeviceGroup(int M, int N, int Px, int Py, const std::vector<int>& devices) : M_(M), N_(N) {
   const int n = Px * Py;
   if ((int)devices.size() != n) throw std::runtime_error("DeviceGroup: need one device per rank");
   grid_ = make_grid(M, N);
+  double t_prev = trace_now();
   bootstrap_devices(devices);
+  trace_init("bootstrap (again)", t_prev);
   // one Solver per device (arena allocation and zeroing), all devices at once
   solvers_.resize(n);
   streams_.resize(n);
@@ -91,10 +107,12 @@ DeviceGroup::DeviceGroup(int M, int N, int Px, int Py, const std::vector<int>& d
     PB_CUDA_CHECK(cudaSetDevice(devices[r]));
     PB_CUDA_CHECK(cudaStreamCreateWithFlags(&streams_[r], cudaStreamNonBlocking));
   });
+  trace_init("solvers (arenas)", t_prev);
   for (int r = 0; r < n; ++r)
     for (int q = 0; q < n; ++q)
       if (q != r) solvers_[r]->set_peer_base(q, solvers_[q]->arena(0));
   parallel_for_devices(n, [&](int r) { solvers_[r]->finalize(); });
+  trace_init("finalize (maps, contexts)", t_prev);
 }
 
 DeviceGroup::~DeviceGroup() {
@@ -108,9 +126,12 @@ DeviceGroup::~DeviceGroup() {
 void DeviceGroup::solve(const SolveOptions& opt, pb_stats* out) {
   if (opt.method != kMethodPersistent && opt.method != kMethodPersistentLdg && solvers_.size() > 1)
     throw std::runtime_error("DeviceGroup: only the persistent method runs on several devices");
+  double t_prev = trace_now();
   for (size_t r = 0; r < solvers_.size(); ++r) solvers_[r]->enqueue(opt, streams_[r]);
+  trace_init("enqueue (first: module load)", t_prev);
   std::vector<pb_stats> st(solvers_.size());
   for (size_t r = 0; r < solvers_.size(); ++r) solvers_[r]->collect(streams_[r], &st[r]);
+  trace_init("collect (device time)", t_prev);
   if (!out) return;
   *out = st[0];
   for (size_t r = 1; r < st.size(); ++r) {
