@@ -32,6 +32,8 @@ PROGRAMS = {
     "stage2_mpi": ("stage2-mpi/poisson_mpi_decomp.cpp", "mpi", []),
     "stage3_hybrid": ("stage3-mpi+openmp/main_hybrid.cpp", "mpi_omp", []),
     "poisson_mpi_cuda": ("stage4-mpi+cuda/poisson_mpi_cuda2.cu", "cuda", []),
+    # micro-benchmark driver (baseline/ref_comm_bench.cu) around the unmodified stage-4 source, which it #includes
+    "ref_comm_bench": ("stage4-mpi+cuda/poisson_mpi_cuda2.cu", "cuda_bench", []),
 }
 
 
@@ -59,7 +61,10 @@ def build(names=None, verbose=False) -> dict:
                 SHIM / "mpishim.cpp").stat().st_mtime:
             results[name] = "up to date"
             continue
-        if kind == "cuda":
+        if kind == "cuda_bench":
+            cmd = ["nvcc", "-O3", "-std=c++11", "-arch=sm_100", "-DPB_SHIM_WITH_CUDA", f"-I{SHIM}", f"-I{SRC}",
+                   str(HERE / "ref_comm_bench.cu"), str(SHIM / "mpishim.cpp"), "-o", str(out), "-lrt"]
+        elif kind == "cuda":
             cmd = ["nvcc", "-O3", "-std=c++11", "-arch=sm_100", "-DPB_SHIM_WITH_CUDA", f"-I{SHIM}", str(src),
                    str(SHIM / "mpishim.cpp"), "-o", str(out), "-lrt"]
         else:

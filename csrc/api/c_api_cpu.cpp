@@ -6,6 +6,9 @@
 #include "../../include/poisson_b200.h"
 #include "../core/decomp.h"
 #include "../core/problem.h"
+#include <algorithm>
+
+#include "../cpu/dist_solver.h"
 #include "../cpu/oracle.h"
 #include "error.h"
 
@@ -117,6 +120,41 @@ int pb_cpu_solve(int M, int N, int norm, double delta, long long max_iter, int t
     pb::SolveStats st;
     pb::cpu_solve(M, N, opt, w_out, &st);
     if (stats) fill_stats(st, stats);
+    return 0;
+  } catch (const std::exception& e) {
+    pb::set_last_error(e.what());
+    return -2;
+  }
+}
+
+int pb_cpu_dist_solve(int M, int N, int Px, int Py, int rank, const char* job, int norm, double delta, long long max_iter,
+                      int threads, double* w_block, pb_stats* stats) {
+  try {
+    if (M < 2 || N < 2 || Px < 1 || Py < 1 || rank < 0 || rank >= Px * Py || !job) {
+      pb::set_last_error("pb_cpu_dist_solve: invalid arguments");
+      return -1;
+    }
+    const pb::ProcGrid pg{Px, Py};
+    size_t line = 0;
+    for (int r = 0; r < Px * Py; ++r) {
+      const pb::LocalBlock b = pb::make_local_block(M, N, pg, r);
+      line = std::max(line, (size_t)std::max(b.nx, b.ny));
+    }
+    pb::ShmComm comm(job, rank, Px * Py, line);
+    pb::CpuOptions opt;
+    opt.norm = norm;
+    opt.delta = delta;
+    opt.max_iter = max_iter;
+    opt.threads = threads;
+    pb::SolveStats st;
+    pb::DistTimes tm;
+    pb::cpu_dist_solve(M, N, pg, comm, opt, w_block, &st, &tm);
+    if (stats) {
+      fill_stats(st, stats);
+      stats->t_assemble = tm.assemble;
+      stats->t_comm = tm.comm;
+      stats->t_iterations = st.seconds - tm.assemble;
+    }
     return 0;
   } catch (const std::exception& e) {
     pb::set_last_error(e.what());

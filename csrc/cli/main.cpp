@@ -17,6 +17,9 @@
 #include <string>
 #include <vector>
 
+#include <sys/wait.h>
+#include <unistd.h>
+
 #include "../../include/poisson_b200.h"
 
 namespace {
@@ -28,7 +31,8 @@ double now_s() {
 void usage() {
   std::cout << "usage: poisson_b200 [M N] [--gpus G] [--grid PxxPy|reference|auto] [--virtual] [--norm weighted|unweighted]\n"
                "                    [--delta D] [--max-iter K] [--method persistent|step_fused|step_classic]\n"
-               "                    [--fast-div] [--dump FILE] [--stage 0|1|4] [--threads T[,T...]] [--grids MxN[,MxN...]]\n"
+               "                    [--fast-div] [--dump FILE] [--stage 0|1|2|3|4] [--ranks P] [--threads T[,T...]]\n"
+               "                    [--grids MxN[,MxN...]]\n"
                "                    [--quiet-extras]\n";
 }
 
@@ -74,7 +78,7 @@ void print_extras(const pb_stats& st) {
 int main(int argc, char** argv) {
   const double t_launch = now_s();
   double t_program_start = t_launch;
-  int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4;
+  int M = 40, N = 40, gpus = 1, Px = 0, Py = 0, stage = 4, ranks = 1;
   std::vector<int> thread_list{1}, grid_list;
   bool virt = false, extras = true, ref_grid = false;
   std::string dump, method = "persistent";
@@ -111,6 +115,7 @@ int main(int argc, char** argv) {
     else if (a == "--dump") dump = next();
     else if (a == "--stage") stage = std::atoi(next().c_str());
     else if (a == "--threads") thread_list = parse_int_list(next());
+    else if (a == "--ranks") ranks = std::atoi(next().c_str());
     else if (a == "--grids") grid_list = parse_int_list(next());
     else if (a == "--quiet-extras") extras = false;
     else if (a == "-h" || a == "--help") { usage(); return 0; }
@@ -122,6 +127,53 @@ int main(int argc, char** argv) {
   }
   if (method == "step_fused") opt.method = PB_METHOD_STEP_FUSED;
   else if (method == "step_classic") opt.method = PB_METHOD_STEP_CLASSIC;
+
+  // ---- distributed CPU stages (2: "pure MPI", 3: "MPI + OpenMP"): this program is its own launcher ----
+  if (stage == 2 || stage == 3) {
+    // `--ranks P` forks P - 1 further processes; all of them attach to one shared-memory segment named after this
+    // process (csrc/runtime/shm_comm.h) and run the C++ host loop (csrc/cpu/dist_solver.cpp).  Rank 0 prints the
+    // reference's report (S2:476-497, S3:486-507).
+    if (ranks < 1) { usage(); return 2; }
+    if (Px == 0) pb_choose_proc_grid(ranks, &Px, &Py);
+    if (Px * Py != ranks) {
+      std::cerr << "error: --grid " << Px << "x" << Py << " does not match " << ranks << " ranks\n";
+      return 2;
+    }
+    const int threads = stage == 3 ? thread_list.front() : 1;
+    const std::string job = std::to_string((long long)getpid());
+    int my_rank = 0;
+    std::vector<pid_t> children;
+    for (int r = 1; r < ranks; ++r) {
+      const pid_t pid = fork();
+      if (pid < 0) { std::cerr << "error: fork failed\n"; return 1; }
+      if (pid == 0) { my_rank = r; children.clear(); break; }
+      children.push_back(pid);
+    }
+    if (my_rank == 0) {
+      if (stage == 3) std::cout << "MPI/OpenMP run with " << ranks << " MPI processes; M=" << M << ", N=" << N << std::endl;
+      else std::cout << "Pure MPI 2D run with " << ranks << " processes; M=" << M << ", N=" << N << std::endl;
+    }
+    pb_stats st{};
+    const int rc = pb_cpu_dist_solve(M, N, Px, Py, my_rank, job.c_str(), opt.norm, opt.delta, opt.max_iter, threads, nullptr, &st);
+    if (my_rank != 0) _exit(rc == 0 ? 0 : 1);
+    int bad = rc != 0;
+    for (pid_t c : children) {
+      int status = 0;
+      waitpid(c, &status, 0);
+      bad |= !(WIFEXITED(status) && WEXITSTATUS(status) == 0);
+    }
+    if (bad) { std::cerr << "error: " << pb_last_error() << "\n"; return 1; }
+    if (st.status == PB_STATUS_CONVERGED)
+      std::cout << "Converged after " << st.iters << " iterations (||w(k+1)-w(k)|| < " << opt.delta << ").\n";
+    std::cout << "M=" << M << ", N=" << N << " | Iter=" << st.iters << " | Time=" << std::fixed << std::setprecision(6)
+              << st.seconds << " s\n";
+    std::cout.flush();
+    if (extras) {
+      print_extras(st);
+      std::printf("   Halo exchange + all-reduce time (max over ranks) ~ %.6f s\n", st.t_comm);
+    }
+    return 0;
+  }
 
   // ---- CPU stages ----
   if (stage == 0 || stage == 1) {

@@ -41,9 +41,9 @@ typedef struct pb_stats {
   /* the reference's five buckets (S4:695-700), fed from device-side clocks on the GPU paths */
   double t_gpu;      /* stencil + update phases */
   double t_copy;     /* host<->device copies inside the solve (0 on the fused paths) */
-  double t_comm;     /* waiting for halo data / cross-GPU reductions */
-  double t_precond;  /* share of t_gpu spent in z = r/D (attributed) */
-  double t_dot;      /* reduction phases */
+  double t_comm;     /* waiting for / unpacking the neighbours' halo records (CPU stages: halo exchanges + all-reduces) */
+  double t_precond;  /* 0 on the fused paths: z = r/D is a few instructions inside both phases, it has no time of its own */
+  double t_dot;      /* the in-kernel reductions, cross-GPU part included */
   double t_assemble; /* coefficient / right-hand-side assembly */
   double t_iterations; /* the PCG loop alone (CUDA events) */
   double sum_e2_in_D; /* raw sums of squared errors over the local ranks, for cross-process reduction */
@@ -86,6 +86,15 @@ double pb_exact(double x, double y);
 int pb_cpu_solve(int M, int N, int norm, double delta, long long max_iter, int threads,
                  int signed_breakdown, double* w_out /* (M+1)*(N+1) or NULL */, pb_stats* stats);
 int pb_cpu_error_report(int M, int N, const double* w, pb_stats* stats);
+/* Distributed CPU solver, host loop in C++ (replaces solve_mpi of stages 2 and 3: S2:356-460, S3:364-470).
+ * Collective over the Px*Py processes of one node that pass the same `job` string (the transport is a POSIX
+ * shared-memory segment named after it, csrc/runtime/shm_comm.h; the image has no MPI): this process is `rank` and
+ * owns block `rank` of the grid.  threads > 1 = the MPI + OpenMP stage.  w_block, if not NULL, receives this rank's
+ * block in the padded layout of pb_local_block ((nx+2) x pitch doubles).  stats are global (same on every rank):
+ * seconds = barrier-to-barrier wall time of assembly + iterations, t_comm = halo exchanges + all-reduces (max over
+ * ranks). */
+int pb_cpu_dist_solve(int M, int N, int Px, int Py, int rank, const char* job, int norm, double delta, long long max_iter,
+                      int threads, double* w_block /* or NULL */, pb_stats* stats);
 
 /* ---- CPU local-block operations for the distributed CPU backend (replaces the per-rank loops of
  *      stages 2/3: S2:124-232, S2:418-456) ---- */

@@ -30,6 +30,8 @@ NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-rd
 LIB_SOURCES = [
     "core/decomp.cpp",
     "cpu/oracle.cpp",
+    "cpu/dist_solver.cpp",
+    "runtime/shm_comm.cpp",
     "api/c_api_cpu.cpp",
     "cuda/assemble.cu",
     "cuda/step_kernels.cu",

@@ -102,6 +102,8 @@ def _declare(lib: C.CDLL) -> None:
         "pb_cpu_solve": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_double, C.c_longlong, C.c_int, C.c_int, vp,
                                    C.POINTER(Stats)]),
         "pb_cpu_error_report": (C.c_int, [C.c_int, C.c_int, vp, C.POINTER(Stats)]),
+        "pb_cpu_dist_solve": (C.c_int, [C.c_int] * 5 + [C.c_char_p, C.c_int, C.c_double, C.c_longlong, C.c_int, vp,
+                                                         C.POINTER(Stats)]),
         "pb_cpu_assemble_local": (C.c_int, [C.c_int, C.c_int, C.POINTER(Block), vp, vp, vp, vp, C.c_int]),
         "pb_cpu_apply_A_local": (C.c_double, [C.c_int, C.c_int, C.POINTER(Block), vp, vp, vp, vp, C.c_int]),
         "pb_cpu_update_wr_local": (C.c_int, [C.POINTER(Block), vp, vp, vp, vp, vp, C.c_double, dp, C.c_int]),

@@ -37,7 +37,7 @@ def _exchange(sends: dict, recvs: dict):
 
 
 class CollectiveSolver:
-    def __init__(self, M: int, N: int, grid=None, device: str = "cuda", threads: int = 1):
+    def __init__(self, M: int, N: int, grid=None, device: str = "cuda", threads: int = 1, native_cpu: bool = True):
         self.rank, self.world = world_info()
         self.Px, self.Py = parse_grid(grid, self.world)
         self.M, self.N = M, N
@@ -64,6 +64,10 @@ class CollectiveSolver:
             shape = (self.blk.nx + 2, self.blk.pitch)
             self.f = {k: torch.zeros(shape, dtype=torch.float64) for k in ("w", "r", "p", "Ap", "a", "b", "D")}
             self.nblk = native_block(self.blk)
+            # The host loop runs in C++ over the shared-memory transport (csrc/cpu/dist_solver.cpp) when every rank
+            # sits on this node; gloo and the Python loop below remain for runs that span nodes.
+            self.native_cpu = native_cpu and self._single_node()
+            self._jobs = 0
 
     # ------------------------------------------------------------------------------------------
     def solve(self, norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1, check_every: int = 16,
@@ -73,6 +77,8 @@ class CollectiveSolver:
         if self.kind == "cuda":
             res = self._solve_cuda(norm, delta, max_iter, check_every, div)
             return combine_reports(res, self.M, self.N, device=f"cuda:{self.gpu.device}")
+        if self.native_cpu:
+            return self._solve_cpu_native(norm, delta, max_iter)
         res = self._solve_cpu(norm, delta, max_iter)
         return combine_reports(res, self.M, self.N, device="cpu")
 
@@ -141,6 +147,35 @@ class CollectiveSolver:
             "t_comm": 0.0, "t_precond": 0.0, "t_dot": 0.0, "launches": launches,
             "status_name": {0: "max_iter", 1: "converged", 2: "breakdown"}.get(ctl["status"], "?"),
         }
+
+    # ---- native CPU solver (C++ host loop, shared-memory transport) ---------------------------
+    def _single_node(self) -> bool:
+        if self.world == 1:
+            return True
+        import socket
+
+        hosts = [None] * self.world
+        dist.all_gather_object(hosts, socket.gethostname())
+        return len(set(hosts)) == 1
+
+    def _solve_cpu_native(self, norm, delta, max_iter):
+        import os
+
+        from ..ops.gpu import NORMS, STATUS
+
+        self._jobs += 1
+        job = [f"{os.getpid()}_{self._jobs}"]  # rank 0's name for the shared-memory segment of this solve
+        if self.world > 1:
+            dist.broadcast_object_list(job, src=0)
+        st = _native.Stats()
+        _native.check(_native.lib().pb_cpu_dist_solve(self.M, self.N, self.Px, self.Py, self.rank, job[0].encode(),
+                                                      NORMS[norm], delta, max_iter, self.threads,
+                                                      self.f["w"].data_ptr(), C.byref(st)), "pb_cpu_dist_solve")
+        res = st.as_dict()
+        res["status_name"] = STATUS.get(st.status, "?")
+        res["launches"] = 0
+        res["host_loop"] = "c++ (shared memory)"
+        return res
 
     # ---- gloo CPU solver --------------------------------------------------------------------
     def _halo_cpu(self):

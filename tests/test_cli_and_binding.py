@@ -112,3 +112,24 @@ def test_torch_binding():
     rep2, w2 = ext.solve(160, 160, 2, 2)
     assert rep2["iters"] == 183
     assert torch.allclose(w, w2, rtol=0, atol=1e-12)
+
+
+def test_cli_distributed_cpu_stages_fork_their_own_ranks():
+    """--stage 2 / 3: the CLI is its own launcher (fork + shared-memory transport, C++ host loop) and prints the
+    reference's stage-2 / stage-3 report (S2:476-497, S3:486-507)."""
+    import subprocess
+
+    from poisson_ellipse_openmp_mpi_cuda_b200 import _build
+
+    _build.build_native()
+    for stage, ranks, extra, banner in [(2, 4, [], "Pure MPI 2D run with 4 processes; M=160, N=160"),
+                                        (3, 2, ["--threads", "2"], "MPI/OpenMP run with 2 MPI processes; M=160, N=160"),
+                                        (2, 6, ["--grid", "3x2"], "Pure MPI 2D run with 6 processes; M=160, N=160")]:
+        out = subprocess.run([str(_build.CLI_PATH), "160", "160", "--stage", str(stage), "--ranks", str(ranks), *extra],
+                             capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0, out.stderr
+        lines = out.stdout.splitlines()
+        assert lines[0] == banner
+        assert lines[1] == "Converged after 183 iterations (||w(k+1)-w(k)|| < 1e-06)."
+        assert lines[2].startswith("M=160, N=160 | Iter=183 | Time=")
+        assert "L2 error vs analytic (in D)  ~ 8.9567" in out.stdout
