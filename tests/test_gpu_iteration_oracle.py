@@ -127,3 +127,21 @@ def test_headline_grid_50_iterations_against_step_kernels():
     assert ra["diff_norm"] == pytest.approx(rb["diff_norm"], rel=1e-9)
     assert float((wa - wb).abs().max()) <= 1e-12 * float(wb.abs().max())
     s.close()
+
+
+def test_soak_200_solves_on_virtual_ranks():
+    """200 solves in a row on 2 x 2 virtual ranks (halo records, proxy fences, record-star reductions with their
+    sequence numbers running on across launches): every one must give the same iteration count and the same bits.
+    (compute-sanitizer is closed on the GPU pool -- profiles/r2/sanitizer/ -- so protocol slips are hunted with
+    repetition and oracles instead.)"""
+    s = _solver(160, 160, 2, 2)
+    first = None
+    for i in range(200):
+        r = s.solve(error_report=False, watchdog_s=5.0)
+        assert r["iters"] == 183 and r["status_name"] == "converged", (i, r)
+        w = s.solution_host()
+        if first is None:
+            first = w.clone()
+        else:
+            assert torch.equal(w, first), i
+    s.close()
