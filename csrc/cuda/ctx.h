@@ -100,7 +100,7 @@ struct RankCtx {
   int ll_cap;
   unsigned long long* nbr_ll[4];
   int nbr_ll_cap[4];
-  const void* tmaps;  // CUtensorMap[2][12] in device memory (TMA persistent kernel), see persistent_tma.cu
+  const void* tmaps;  // CUtensorMap[kMapVariants][kMapsPerVariant] in device memory (TMA persistent kernel)
   int sys_scope;  // 1: some peer lives on another device, fences must be system-wide
   // tiling of the block for the stencil phase
   int tiles_x, tiles_y;
@@ -116,5 +116,6 @@ inline size_t halo_ll_offset(const LocalBlock& b) { return kHeaderBytes + 8 * b.
 inline size_t halo_ll_bytes(const LocalBlock& b) { return (size_t)4 * 2 * ll_capacity(b) * 2 * sizeof(unsigned long long); }
 inline size_t arena_bytes(const LocalBlock& b) { return halo_ll_offset(b) + halo_ll_bytes(b); }
 constexpr int kMapsPerVariant = 16;  // tensor-map slots per tile height (12 used, see persistent_tma.cu)
+constexpr int kMapVariants = 3;      // box heights 32, 16 and 64 rows
 
 }  // namespace pb

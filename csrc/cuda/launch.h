@@ -23,7 +23,9 @@ size_t persistent_smem_bytes();
 int persistent_max_ctas_per_sm(int div);
 cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int div, cudaStream_t stream);
 
-// KP-TMA (persistent_tma.cu): tile_rows is 32 (2 stages) or 16 (4 stages)
+// KP-TMA (persistent_tma.cu): tile_rows is 32 (2 stages), 16 (4 stages) or 64 (32-row tiles, pairs of full
+// constant-coefficient tiles merged into tall items)
+int persistent_tma_max_items();  // work items one CTA can hold
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
                                   int l2_hints, bool compressed, bool recompute_ap, cudaStream_t stream);
 cudaError_t launch_tma_probe(const void* dmaps, const void* hmaps, int idx, int mode, int x, int y, unsigned int nbytes,

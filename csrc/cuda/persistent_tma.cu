@@ -33,7 +33,19 @@
 namespace pb {
 
 enum TmaMap : int { kMapRExt = 0, kMapDExt, kMapP0Ext, kMapP1Ext, kMapA, kMapB, kMapW, kMapP0, kMapP1, kMapR, kMapAp, kMapD };
-constexpr int kMaxTileClass = 1024;  // tiles per CTA whose class is cached in shared memory (more: treated as mixed)
+constexpr int kMaxItems = 768;  // work items per CTA (the host refuses blocks that would need more)
+
+// One unit of work of a CTA in both phases: a tile of TX rows, or (tall) two vertically adjacent full tiles with the
+// same constant coefficients that travel and are processed as one 2 TX x TY tile.  A tall item halves the per-tile
+// fixed cost of a phase (issue path, barrier waits, mbarrier wait: about 1000 of the 3300 cycles a 32 x 64 tile of
+// phase AB takes) for the constant-coefficient tiles that make up all but a few per cent of a large block.
+struct TileItem {
+  unsigned short li0, lj0;  // first owned node
+  unsigned char flags;      // bits 0-1 coefficient class (0 inside, 1 outside, 2 mixed), bit 2 Ap recomputed, bit 3 tall
+  unsigned char pad;
+};
+constexpr int kItemRecomp = 4, kItemTall = 8;
+constexpr int kTallVariant = 2;  // tensor-map set with boxes of 2 * 32 rows
 
 template <int TX>
 struct TmaCfg {
@@ -52,7 +64,18 @@ struct TmaCfg {
   static constexpr int kStageAB = 3 * kExtBytes + kABytes + kBBytes;
   static constexpr int kStageC = 5 * kTileBytes;
   static_assert(kOffCPe + kExtBytes <= kStageC, "recompute layout must fit into a phase-C stage");
-  static constexpr int kStageBytes = kStageAB > kStageC ? kStageAB : kStageC;
+  // tall items (TX = 32 only; always constant coefficients and recomputed Ap): phase AB r | p, phase C w | r | p_new,
+  // boxes of 2 TX (+ 2) rows
+  static constexpr bool kTall = TX == 32;
+  static constexpr int ER2 = 2 * TX + 2;
+  static constexpr int kExtBytes2 = ((ER2 * EC * 8 + 127) / 128) * 128;
+  static constexpr int kTileBytes2 = 2 * kTileBytes;
+  static constexpr int kStageTall = kTall ? 2 * kTileBytes2 + kExtBytes2 : 0;  // phase C is the larger one
+  static_assert(2 * kExtBytes2 <= 2 * kTileBytes2 + kExtBytes2, "tall phase-AB stage must fit");
+  static constexpr uint32_t kTxTallAB = 2u * ER2 * EC * 8u;
+  static constexpr uint32_t kTxTallC = 2u * (uint32_t)kTileBytes2 + 1u * ER2 * EC * 8u;
+  static constexpr int kStage32 = kStageAB > kStageC ? kStageAB : kStageC;
+  static constexpr int kStageBytes = kStage32 > kStageTall ? kStage32 : kStageTall;
   static constexpr int kStages = TX >= 32 ? 2 : 4;
   // transaction bytes = full boxes, out-of-bounds parts included
   static constexpr uint32_t kTxABCore = 2u * ER * EC * 8u;                                       // r, p
@@ -67,13 +90,13 @@ struct TmaCfg {
 template <int TX, int DIV, bool CC>
 __global__ void __launch_bounds__(kThreads, 1)
 pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints,
-                          int recompute_ap) {
+                          int recompute_ap, int tall_mode) {
   using Cfg = TmaCfg<TX>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
   __shared__ double s_red[80];
   __shared__ __align__(8) uint64_t s_bar[S];
-  __shared__ unsigned char s_tclass[kMaxTileClass];
+  __shared__ TileItem s_items[kMaxItems];
   __shared__ int s_filled[S];  // per stage: ring cells were unpacked for the tile in flight (thread 0 only)
   __shared__ volatile int s_abort;  // some thread's TMA wait timed out; read after a barrier, so CTA-uniform
   __shared__ unsigned long long s_wd_limit;  // device-side wait limit in ns (kept out of the registers)
@@ -106,16 +129,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(c.tmaps) + map_variant * kMapsPerVariant;
 
   Control* ctl = c.ctl;
-  const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + TX - 1) / TX;
+  const CUtensorMap* maps_tall = reinterpret_cast<const CUtensorMap*>(c.tmaps) + kTallVariant * kMapsPerVariant;
+  // The block is cut into "super-tiles" of srows x TY nodes, srows = 2 TX when tall items are allowed, else TX;
+  // super-tile t belongs to CTA t mod ncta in both phases.
+  const bool tall_ok = Cfg::kTall && tall_mode != 0 && recompute_ap != 0;
+  const int srows = tall_ok ? 2 * TX : TX;
+  const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + srows - 1) / srows;
   const int ntiles = tiles_x * tiles_y;
-  const int nmine = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
-  // Tile order: row-major, except that the last tile row is visited right after the first one.  The tiles
-  // that store halo rows for the x-neighbours (phase C) and the tiles that need the neighbours' rows
-  // (phase AB) then come first on both sides, so the NVLink latency of the halo records hides behind the
-  // remaining tiles instead of sitting in front of a reduction.  (Enumerating the
-  // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
+  const int nsuper = cta < ntiles ? (ntiles - cta + ncta - 1) / ncta : 0;
   const bool has_nbr = c.nbr_r[0] || c.nbr_r[1] || c.nbr_r[2] || c.nbr_r[3];
-  const int npre = min(S - 1, nmine);  // tiles of a phase that are issued ahead of the phase
   const bool timing = threadIdx.x == 0;  // every CTA keeps its own phase clocks; CTA 0's go into the report
   const int S_pitch = c.pitch;
 
@@ -146,21 +168,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 
   unsigned int n_issued = 0, n_consumed = 0;  // uniform across the CTA
 
-  auto tile_origin = [&](int j, int& li0, int& lj0) {
-    const int t = cta + j * ncta;
-    int tx = t / tiles_y;
-    const int ty = t - tx * tiles_y;
-    if (has_nbr && tiles_x > 2) tx = tx == 0 ? 0 : (tx == 1 ? tiles_x - 1 : tx - 1);
-    li0 = 1 + tx * TX;
-    lj0 = 1 + ty * TY;
-  };
-  // Tile classes: 0 = every cell of the tile and its ring is "inside" (a = b = 1, D = diag_in), 1 = all
-  // "outside" (1/eps, diag_out), 2 = mixed (full coefficient boxes).  One pass over the class bytes per launch.
-  if constexpr (CC) {
-    for (int j = 0; j < nmine && j < kMaxTileClass; ++j) {
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
-      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+  // ---- work items of this CTA (one pass over the class bytes per launch) ----
+  // Coefficient classes: 0 = every cell of the tile and its ring is "inside" (a = b = 1, D = diag_in), 1 = all
+  // "outside" (1/eps, diag_out), 2 = mixed (full coefficient boxes).  Full tiles with constant coefficients can get Ap
+  // in phase C by evaluating the stencil again on the p_new box (the same device function on the same operands: the
+  // same bits), which saves the store and the reload of Ap.
+  int nmine = 0;  // items; uniform across the CTA
+  {
+    auto classify = [&](int li0, int lj0, int cx, int cy) -> int {
+      if constexpr (!CC) return 2;
       bool all_in = true, all_out = true;
       for (int e = threadIdx.x; e < (cx + 2) * (cy + 2); e += kThreads) {
         const int row = e / (cy + 2), col = e - row * (cy + 2);
@@ -170,16 +186,47 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         all_out = all_out && (b == 0x15u);
       }
       const int in = __syncthreads_and(all_in ? 1 : 0), out = __syncthreads_and(all_out ? 1 : 0);
-      if (threadIdx.x == 0) s_tclass[j] = in ? 0 : (out ? 1 : 2);
+      return in ? 0 : (out ? 1 : 2);
+    };
+    auto add_item = [&](int li0, int lj0, int flags) {
+      if (threadIdx.x == 0 && nmine < kMaxItems) {
+        s_items[nmine].li0 = (unsigned short)li0, s_items[nmine].lj0 = (unsigned short)lj0;
+        s_items[nmine].flags = (unsigned char)flags, s_items[nmine].pad = 0;
+      }
+      ++nmine;
+    };
+    for (int j = 0; j < nsuper; ++j) {
+      const int t = cta + j * ncta;
+      int tx = t / tiles_y;
+      const int ty = t - tx * tiles_y;
+      // Row order: first, last, second, ...: the tiles that store halo rows for the x-neighbours (phase C) and the
+      // tiles that need the neighbours' rows (phase AB) then come first on both sides, so the NVLink latency of the
+      // halo records hides behind the remaining tiles instead of sitting in front of a reduction.  (Enumerating the
+      // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
+      if (has_nbr && tiles_x > 2) tx = tx == 0 ? 0 : (tx == 1 ? tiles_x - 1 : tx - 1);
+      const int li0 = 1 + tx * srows, lj0 = 1 + ty * TY;
+      const int cy = min(TY, c.ny - lj0 + 1);
+      const int cx0 = min(TX, c.nx - li0 + 1);
+      const int m0 = classify(li0, lj0, cx0, cy);
+      const bool full0 = cx0 == TX && cy == TY;
+      const bool second = srows > TX && li0 + TX <= c.nx;
+      int m1 = 2, cx1 = 0;
+      if (second) {
+        cx1 = min(TX, c.nx - (li0 + TX) + 1);
+        m1 = classify(li0 + TX, lj0, cx1, cy);
+      }
+      if (second && full0 && cx1 == TX && m0 != 2 && m0 == m1) {
+        add_item(li0, lj0, m0 | kItemRecomp | kItemTall);
+      } else {
+        add_item(li0, lj0, m0 | ((recompute_ap && m0 != 2 && full0) ? kItemRecomp : 0));
+        if (second) add_item(li0 + TX, lj0, m1 | ((recompute_ap && m1 != 2 && cx1 == TX && cy == TY) ? kItemRecomp : 0));
+      }
     }
+    nmine = min(nmine, kMaxItems);  // the host sizes the launch so that this never cuts anything off
     __syncthreads();
   }
-  auto tile_mode = [&](int j) -> int { return (CC && j < kMaxTileClass) ? (int)s_tclass[j] : 2; };
-  // Full tiles with constant coefficients can get Ap in phase C by evaluating the stencil again on the p_new box
-  // (the same device function on the same operands: the same bits), which saves the store and the reload of Ap.
-  auto tile_recomputes = [&](int j, int li0, int lj0) -> bool {
-    return recompute_ap && tile_mode(j) != 2 && li0 + TX - 1 <= c.nx && lj0 + TY - 1 <= c.ny;
-  };
+  const int npre = min(S - 1, nmine);  // items of a phase that are issued ahead of the phase
+  auto item_rows = [&](int flags) -> int { return (flags & kItemTall) ? 2 * TX : TX; };
 
   // Halo rows travel as LL records (payload32 | sequence32 word pairs, see ctx.h): the producer needs no fence and
   // no counter, the consumer recognises complete values by their sequence number.  Round k of this launch
@@ -187,8 +234,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const unsigned int hseq = ctl->halo_seq;
   // warp 0: copy the neighbours' r values of round `rounds` for the ring cells of the tile at (li0, lj0) from the
   // halo lines into our r ring; returns whether the tile touches a shared edge at all
-  auto unpack_halo = [&](int li0, int lj0, long long rounds) -> bool {
-    const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+  auto unpack_halo = [&](int li0, int lj0, int rows, long long rounds) -> bool {
+    const int cx = min(rows, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
     const bool touch[4] = {li0 == 1, li0 + cx - 1 == c.nx, lj0 == 1, lj0 + cy - 1 == c.ny};
     const unsigned int want = hseq + (unsigned int)rounds;
     const unsigned long long limit = s_wd_limit;
@@ -235,20 +282,22 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // phase C (p and, for mixed tiles, D, a, b; arms the barrier with the full byte count), part 2 = the r box.
   auto issue_ab_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2, long long rounds) {
     if (threadIdx.x < 32) {
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
+      const TileItem it = s_items[j];
+      const int li0 = it.li0, lj0 = it.lj0, mode = it.flags & 3;
+      const bool tall = (it.flags & kItemTall) != 0;
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
       const int x = kColOff + lj0 - 2, y = li0 - 1;  // even column: 16-byte aligned box start
+      const CUtensorMap* mp = tall ? maps_tall : maps;
       // A tile on a shared edge gets its ring cells filled from the halo lines by the whole warp.  This depends
       // only on the neighbour GPU, so it belongs to part 1 and its latency hides in the reduction that follows.
-      const bool filled = part1 && has_nbr && rounds > 0 && unpack_halo(li0, lj0, rounds);
+      const bool filled = part1 && has_nbr && rounds > 0 && unpack_halo(li0, lj0, item_rows(it.flags), rounds);
       if (part1 && threadIdx.x == 0) {
         if (filled) s_filled[st] = 1;
-        const bool coef = tile_mode(j) == 2;
+        const bool coef = mode == 2;
         fence_proxy_async_smem();
-        mbar_arrive_expect_tx(bar, Cfg::kTxABCore + (coef ? Cfg::kTxABCoef : 0u));
-        tma_load_2d_hint(sb + Cfg::kOffP, maps + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar, pol_keep);
+        mbar_arrive_expect_tx(bar, tall ? Cfg::kTxTallAB : Cfg::kTxABCore + (coef ? Cfg::kTxABCoef : 0u));
+        tma_load_2d_hint(sb + (tall ? Cfg::kExtBytes2 : Cfg::kOffP), mp + (pbuf ? kMapP1Ext : kMapP0Ext), x, y, bar, pol_keep);
         if (coef) {
           tma_load_2d_hint(sb + Cfg::kOffD, maps + kMapDExt, x, y, bar, pol_keep);
           tma_load_2d_hint(sb + Cfg::kOffA, maps + kMapA, x + 2, y + 1, bar, pol_stream);
@@ -262,7 +311,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
             fence_proxy_async();
             s_filled[st] = 0;
           }
-          tma_load_2d_hint(sb + Cfg::kOffR, maps + kMapRExt, x, y, bar, pol_keep);
+          tma_load_2d_hint(sb + Cfg::kOffR, mp + kMapRExt, x, y, bar, pol_keep);
         }
       }
     }
@@ -276,13 +325,24 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // were written by other CTAs during phase AB, so that box has to wait for the reduction after it.
   auto issue_c_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2) {
     if (threadIdx.x == 0) {
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
+      const TileItem it = s_items[j];
+      const int li0 = it.li0, lj0 = it.lj0;
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
-      const bool coef = tile_mode(j) == 2;
-      const bool recomp = tile_recomputes(j, li0, lj0);
+      const bool coef = (it.flags & 3) == 2;
+      const bool recomp = (it.flags & kItemRecomp) != 0, tall = (it.flags & kItemTall) != 0;
       const int x = kColOff + lj0, y = li0;
+      if (tall) {  // w | r | p_new with ring, boxes of 2 TX rows
+        if (part1) {
+          fence_proxy_async_smem();
+          mbar_arrive_expect_tx(bar, Cfg::kTxTallC);
+          tma_load_2d_hint(sb, maps_tall + kMapW, x, y, bar, pol_stream);
+          tma_load_2d_hint(sb + Cfg::kTileBytes2, maps_tall + kMapR, x, y, bar, pol_keep);
+        }
+        if (part2)
+          tma_load_2d_hint(sb + 2 * Cfg::kTileBytes2, maps_tall + (pbuf ? kMapP1Ext : kMapP0Ext), x - 2, y - 1, bar, pol_keep);
+        return;
+      }
       if (part1) {
         fence_proxy_async_smem();
         mbar_arrive_expect_tx(bar, recomp ? Cfg::kTxCRecomp : Cfg::kTxCCore + (coef ? Cfg::kTxCCoef : 0u));
@@ -373,28 +433,30 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     for (int j = 0; j < nmine; ++j) {
       if (j + S - 1 < nmine) issue_ab(j + S - 1, cur, k - 1);
       unsigned char* sb = wait_stage();
+      const TileItem item = s_items[j];  // CTA-uniform
+      const int li0 = item.li0, lj0 = item.lj0, tmode = item.flags & 3;
+      const bool tall = (item.flags & kItemTall) != 0;
+      const int rows = tall ? 2 * TX : TX;  // rows of the box in shared memory (a tall item is always full)
       const double* s_r = reinterpret_cast<const double*>(sb + Cfg::kOffR);
-      double* s_p = reinterpret_cast<double*>(sb + Cfg::kOffP);
+      double* s_p = reinterpret_cast<double*>(sb + (tall ? Cfg::kExtBytes2 : Cfg::kOffP));
       const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffD);
       const double* s_a = reinterpret_cast<const double*>(sb + Cfg::kOffA);
       const double* s_b = reinterpret_cast<const double*>(sb + Cfg::kOffB);
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
-      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
-      const bool full = (cx == TX) && (cy == TY);
-      const int tmode = tile_mode(j);  // CTA-uniform
+      const int cx = min(rows, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+      const bool full = (cx == rows) && (cy == TY);
       const double cf = tmode == 1 ? inv_eps : 1.0;  // uniform tiles: every face coefficient
       const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
-      const bool keep_ap = !tile_recomputes(j, li0, lj0);  // phase C reloads Ap (else it evaluates the stencil again)
+      const bool keep_ap = (item.flags & kItemRecomp) == 0;  // phase C reloads Ap (else it evaluates the stencil again)
+      const int nhalf = rows / TX;  // full tiles are processed in slices of TX rows, 4 (TX = 32) nodes per thread each
 
       // The two halves of the phase on one tile.  `uniform` is a compile-time tag, so the constant-coefficient
       // path carries no shared-memory coefficient loads and the mixed path no selects.
       auto run_tile = [&](auto uniform) {
         constexpr bool U = decltype(uniform)::value;
         // 1. p_new = r/D + beta p_old on the tile and its ring, in place in shared memory.  The owned cells
-        //    map to threads without any division or validity test (4 cells per thread, unrolled for full
+        //    map to threads without any division or validity test (4 cells per thread and slice, unrolled for full
         //    tiles so that their dependent fp64 chains overlap); the ring (top, bottom, left, right: at most
-        //    2 TY + 2 TX cells) is one extra cell for the first 192 threads.  A cell of shared-memory row `er`,
+        //    2 TY + 2 rows cells) is one extra cell for the first threads.  A cell of shared-memory row `er`,
         //    tile column `ec` (0 = left ring) sits at er * EC + ec + 1 (the box starts one column early).
         auto p_cell = [&](int er, int ec, bool store) {
           const int e = er * EC + ec + 1;
@@ -408,17 +470,19 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           if (full) {
             // same as p_cell(r00 + 8 q + 1, c0 + 1, true), with the index arithmetic hoisted out of the unrolled body
             constexpr int kRows = kThreads / TY;
-            const double* sr = s_r + (r00 + 1) * EC + c0 + 2;
-            double* sp = s_p + (r00 + 1) * EC + c0 + 2;
-            const double* sd = s_D + (r00 + 1) * EC + c0 + 2;
-            double* po = pout + (size_t)(li0 + r00) * S_pitch + (lj0 + c0 + kColOff);
-            const size_t gstep = (size_t)kRows * S_pitch;
+            for (int h = 0; h < nhalf; ++h) {
+              const double* sr = s_r + (h * TX + r00 + 1) * EC + c0 + 2;
+              double* sp = s_p + (h * TX + r00 + 1) * EC + c0 + 2;
+              const double* sd = s_D + (h * TX + r00 + 1) * EC + c0 + 2;
+              double* po = pout + (size_t)(li0 + h * TX + r00) * S_pitch + (lj0 + c0 + kColOff);
+              const size_t gstep = (size_t)kRows * S_pitch;
 #pragma unroll
-            for (int q = 0; q < TX / kRows; ++q) {
-              const double z = U ? div_known<DIV>(sr[q * kRows * EC], dg, rc) : div_var<DIV>(sr[q * kRows * EC], sd[q * kRows * EC]);
-              const double v = fma(beta, sp[q * kRows * EC], z);
-              sp[q * kRows * EC] = v;
-              po[q * gstep] = v;
+              for (int q = 0; q < TX / kRows; ++q) {
+                const double z = U ? div_known<DIV>(sr[q * kRows * EC], dg, rc) : div_var<DIV>(sr[q * kRows * EC], sd[q * kRows * EC]);
+                const double v = fma(beta, sp[q * kRows * EC], z);
+                sp[q * kRows * EC] = v;
+                po[q * gstep] = v;
+              }
             }
           } else if (c0 < cy) {
             for (int r0 = r00; r0 < cx; r0 += kThreads / TY) p_cell(r0 + 1, c0 + 1, true);
@@ -427,8 +491,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           if (threadIdx.x < 2 * TY) {
             const int side = threadIdx.x / TY, cc = threadIdx.x - side * TY;
             if (cc < cy) p_cell(side ? cx + 1 : 0, cc + 1, side ? (li0 + cx - 1 == c.nx) : (li0 == 1));
-          } else if (threadIdx.x < 2 * TY + 2 * TX) {
-            const int t = threadIdx.x - 2 * TY, side = t / TX, rr = t - side * TX;
+          } else if (threadIdx.x < 2 * TY + 2 * rows) {
+            const int t = threadIdx.x - 2 * TY, side = t / rows, rr = t - side * rows;
             if (rr < cx) p_cell(rr + 1, side ? cy + 1 : 0, side ? (lj0 + cy - 1 == c.ny) : (lj0 == 1));
           }
         }
@@ -451,30 +515,32 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         };
         if (full) {
           // same as ab_node(r00 + 8 q + 1), index arithmetic hoisted
-          constexpr int kRows = kThreads / TY, kPer = TX / kRows;  // nodes per thread
+          constexpr int kRows = kThreads / TY, kPer = TX / kRows;  // nodes per thread and slice
           const int r00 = threadIdx.x / TY;
-          const double* sp = s_p + (r00 + 1) * EC + col + 1;
-          const double* sa = s_a + r00 * TY + (col - 1);
-          const double* sb2 = s_b + r00 * BC + (col - 1);
-          double* ap = c.Ap + (size_t)(li0 + r00) * S_pitch + (lj0 - 1 + col + kColOff);
-          const size_t gstep = (size_t)kRows * S_pitch;
-          double v[kPer], pc[kPer];
+          for (int h = 0; h < nhalf; ++h) {
+            const double* sp = s_p + (h * TX + r00 + 1) * EC + col + 1;
+            const double* sa = s_a + (h * TX + r00) * TY + (col - 1);
+            const double* sb2 = s_b + (h * TX + r00) * BC + (col - 1);
+            double* ap = c.Ap + (size_t)(li0 + h * TX + r00) * S_pitch + (lj0 - 1 + col + kColOff);
+            const size_t gstep = (size_t)kRows * S_pitch;
+            double v[kPer], pc[kPer];
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) {
-            const double* s = sp + q * kRows * EC;
-            pc[q] = s[0];
-            double a_c, a_ip, b_c, b_jp;
-            if constexpr (U) {
-              a_c = a_ip = b_c = b_jp = cf;
-            } else {
-              a_c = sa[q * kRows * TY], a_ip = sa[q * kRows * TY + TY];
-              b_c = sb2[q * kRows * BC], b_jp = sb2[q * kRows * BC + 1];
+            for (int q = 0; q < kPer; ++q) {
+              const double* s = sp + q * kRows * EC;
+              pc[q] = s[0];
+              double a_c, a_ip, b_c, b_jp;
+              if constexpr (U) {
+                a_c = a_ip = b_c = b_jp = cf;
+              } else {
+                a_c = sa[q * kRows * TY], a_ip = sa[q * kRows * TY + TY];
+                b_c = sb2[q * kRows * BC], b_jp = sb2[q * kRows * BC + 1];
+              }
+              v[q] = stencil_value<DIV>(K, pc[q], s[-EC], s[EC], s[-1], s[1], a_c, a_ip, b_c, b_jp);
+              if (keep_ap) ap[q * gstep] = v[q];
             }
-            v[q] = stencil_value<DIV>(K, pc[q], s[-EC], s[EC], s[-1], s[1], a_c, a_ip, b_c, b_jp);
-            if (keep_ap) ap[q * gstep] = v[q];
-          }
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) acc_ab = fma(v[q], pc[q], acc_ab);  // same order as the generic loop
+            for (int q = 0; q < kPer; ++q) acc_ab = fma(v[q], pc[q], acc_ab);  // same order as the generic loop
+          }
         } else if (col <= cy) {
           for (int row = threadIdx.x / TY + 1; row <= cx; row += kThreads / TY) {
             double pc;
@@ -535,22 +601,25 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     for (int j = 0; j < nmine; ++j) {
       if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
       unsigned char* sb = wait_stage();
+      const TileItem item = s_items[j];  // CTA-uniform
+      const int li0 = item.li0, lj0 = item.lj0, tmode = item.flags & 3;
+      const bool tall = (item.flags & kItemTall) != 0;
+      const int rows = tall ? 2 * TX : TX;
+      // 32-row items: w | p | r | Ap | D, with recomputed Ap w | - | r | p_new + ring; tall items: w | r | p_new + ring
       const double* s_w = reinterpret_cast<const double*>(sb);
       const double* s_p = reinterpret_cast<const double*>(sb + Cfg::kTileBytes);
-      const double* s_r = reinterpret_cast<const double*>(sb + 2 * Cfg::kTileBytes);
+      const double* s_r = reinterpret_cast<const double*>(sb + (tall ? Cfg::kTileBytes2 : 2 * Cfg::kTileBytes));
       const double* s_Ap = reinterpret_cast<const double*>(sb + 3 * Cfg::kTileBytes);
       const double* s_D = reinterpret_cast<const double*>(sb + Cfg::kOffCD);
-      const double* s_pe = reinterpret_cast<const double*>(sb + Cfg::kOffCPe);  // p_new with ring (recompute only)
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
-      const int cx = min(TX, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
+      const double* s_pe = reinterpret_cast<const double*>(sb + (tall ? 2 * Cfg::kTileBytes2 : Cfg::kOffCPe));  // recompute only
+      const int cx = min(rows, c.nx - li0 + 1), cy = min(TY, c.ny - lj0 + 1);
       const int col = threadIdx.x % TY;
-      const bool full = (cx == TX) && (cy == TY);
-      const int tmode = tile_mode(j);  // CTA-uniform
+      const bool full = (cx == rows) && (cy == TY);
       const double dg = tmode == 1 ? diag_out : diag_in, rc = tmode == 1 ? rcp_out : rcp_in;
       const double cf = tmode == 1 ? inv_eps : 1.0;
-      const bool recomp = tile_recomputes(j, li0, lj0);  // CTA-uniform; implies full and constant coefficients
+      const bool recomp = (item.flags & kItemRecomp) != 0;  // CTA-uniform; implies full and constant coefficients
       const bool edge_tile = has_nbr && (li0 == 1 || li0 + cx - 1 == c.nx || lj0 == 1 || lj0 + cy - 1 == c.ny);
+      const int nhalf = rows / TX;
       auto run_tile = [&](auto uniform) {
         constexpr bool U = decltype(uniform)::value;
         // p_new and Ap of the node in tile row `row` (0-based): reloaded, or the stencil of phase AB again
@@ -601,41 +670,46 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         if (full && !edge_tile) {
           // same as c_node(r00 + 8 q) without the halo stores, index arithmetic hoisted
           constexpr int kRows = kThreads / TY, kPer = TX / kRows;
-          const int r00 = threadIdx.x / TY, e0 = r00 * TY + col;
-          double* pw = c.w + (size_t)(li0 + r00) * S_pitch + (lj0 + col + kColOff);
-          double* pr = c.r + (size_t)(li0 + r00) * S_pitch + (lj0 + col + kColOff);
-          const size_t gstep = (size_t)kRows * S_pitch;
-          double dw[kPer], z[kPer], rn[kPer];
+          const int r00 = threadIdx.x / TY;
+          for (int h = 0; h < nhalf; ++h) {
+            const int e0 = (h * TX + r00) * TY + col;
+            double* pw = c.w + (size_t)(li0 + h * TX + r00) * S_pitch + (lj0 + col + kColOff);
+            double* pr = c.r + (size_t)(li0 + h * TX + r00) * S_pitch + (lj0 + col + kColOff);
+            const size_t gstep = (size_t)kRows * S_pitch;
+            double dw[kPer], z[kPer], rn[kPer];
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) {
-            const int e = e0 + q * kRows * TY;
-            double pc, ap;
-            p_and_ap(r00 + q * kRows, pc, ap);
-            const double w_old = s_w[e];
-            const double w_new = fma(alpha, pc, w_old);
-            rn[q] = fma(-alpha, ap, s_r[e]);
-            if (l2_hints)
-              __stcs(pw + q * gstep, w_new);
-            else
-              pw[q * gstep] = w_new;
-            pr[q * gstep] = rn[q];
-            dw[q] = __dsub_rn(w_new, w_old);
-            z[q] = U ? div_known<DIV>(rn[q], dg, rc) : div_var<DIV>(rn[q], s_D[e]);
-          }
+            for (int q = 0; q < kPer; ++q) {
+              const int e = e0 + q * kRows * TY;
+              double pc, ap;
+              p_and_ap(h * TX + r00 + q * kRows, pc, ap);
+              const double w_old = s_w[e];
+              const double w_new = fma(alpha, pc, w_old);
+              rn[q] = fma(-alpha, ap, s_r[e]);
+              if (l2_hints)
+                __stcs(pw + q * gstep, w_new);
+              else
+                pw[q * gstep] = w_new;
+              pr[q * gstep] = rn[q];
+              dw[q] = __dsub_rn(w_new, w_old);
+              z[q] = U ? div_known<DIV>(rn[q], dg, rc) : div_var<DIV>(rn[q], s_D[e]);
+            }
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) {
-            acc_d = fma(dw[q], dw[q], acc_d);
-            acc_zr = fma(z[q], rn[q], acc_zr);
+            for (int q = 0; q < kPer; ++q) {
+              acc_d = fma(dw[q], dw[q], acc_d);
+              acc_zr = fma(z[q], rn[q], acc_zr);
+            }
           }
         } else if (full) {
           constexpr int kPer = TX / (kThreads / TY);
-          double dw[kPer], z[kPer], rn[kPer];
+          for (int h = 0; h < nhalf; ++h) {
+            double dw[kPer], z[kPer], rn[kPer];
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) c_node(threadIdx.x / TY + q * (kThreads / TY), dw[q], z[q], rn[q]);
+            for (int q = 0; q < kPer; ++q) c_node(h * TX + threadIdx.x / TY + q * (kThreads / TY), dw[q], z[q], rn[q]);
 #pragma unroll
-          for (int q = 0; q < kPer; ++q) {
-            acc_d = fma(dw[q], dw[q], acc_d);
-            acc_zr = fma(z[q], rn[q], acc_zr);
+            for (int q = 0; q < kPer; ++q) {
+              acc_d = fma(dw[q], dw[q], acc_d);
+              acc_zr = fma(z[q], rn[q], acc_zr);
+            }
           }
         } else if (col < cy) {
           for (int row = threadIdx.x / TY; row < cx; row += kThreads / TY) {
@@ -703,14 +777,15 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(ctl) + kCtaTimesOffset) + kCtaTimeWords * cta;
     mine[0] = (double)t_ab, mine[1] = (double)t_c, mine[2] = (double)t_r1, mine[3] = (double)t_r2;
     // tiles of this CTA by what they move per node and iteration (the bench's byte model counts these)
-    int n_recomp = 0, n_mixed = 0;
+    // (a tall item counts as the two tiles it is made of)
+    int n_recomp = 0, n_mixed = 0, n_tiles = 0;
     for (int j = 0; j < nmine; ++j) {
-      int li0, lj0;
-      tile_origin(j, li0, lj0);
-      n_recomp += tile_recomputes(j, li0, lj0) ? 1 : 0;
-      n_mixed += tile_mode(j) == 2 ? 1 : 0;
+      const int f = s_items[j].flags, w = (f & kItemTall) ? 2 : 1;
+      n_tiles += w;
+      n_recomp += (f & kItemRecomp) ? w : 0;
+      n_mixed += (f & 3) == 2 ? 1 : 0;
     }
-    mine[4] = (double)n_recomp, mine[5] = (double)(nmine - n_mixed - n_recomp), mine[6] = (double)n_mixed;
+    mine[4] = (double)n_recomp, mine[5] = (double)(n_tiles - n_mixed - n_recomp), mine[6] = (double)n_mixed;
     mine[7] = (double)s_t_halo;
   }
   if (cta == 0 && threadIdx.x == 0 && tma_ok) {
@@ -741,34 +816,39 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 // ---------------------------------------------------------------------------------------------------
 template <int TX, int DIV, bool CC>
 static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int l2_hints,
-                                  int recompute_ap, cudaStream_t stream) {
+                                  int recompute_ap, int tall, cudaStream_t stream) {
   const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV, CC>;
   const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints, (void*)&recompute_ap};
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints, (void*)&recompute_ap, (void*)&tall};
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
 }
 
 template <int TX, bool CC>
 static cudaError_t launch_div(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int div, int l2_hints,
-                              int recompute_ap, cudaStream_t stream) {
+                              int recompute_ap, int tall, cudaStream_t stream) {
   if (div == kDivTrue)
-    return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, stream);
+    return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, stream);
   if (div == kDivMarkstein)
-    return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, stream);
-  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, stream);
+    return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, stream);
+  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, stream);
 }
 
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
                                   int l2_hints, bool compressed, bool recompute_ap, cudaStream_t stream) {
   const int ra = (compressed && recompute_ap) ? 1 : 0;  // without coefficient classes no tile is known to be constant
-  if (tile_rows == 32)
-    return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, stream)
-                      : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, stream);
-  return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, stream)
-                    : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, stream);
+  // tile_rows: 16, 32, or 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into tall items
+  // (needs the recomputed Ap: a tall phase-C stage has no room for p and Ap boxes)
+  if (tile_rows == 16)
+    return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, stream)
+                      : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, stream);
+  const int tall = (tile_rows == 64 && ra) ? 1 : 0;
+  return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, tall, stream)
+                    : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, 0, stream);
 }
+
+int persistent_tma_max_items() { return kMaxItems; }
 
 // Debug / unit-test probe: one box load through a tensor map at (x, y) into shared memory, copied out to
 // `out` (nbytes), out_status = 1 on completion, 2 on timeout.  mode 0: map in global memory; mode 1: same,

@@ -46,7 +46,7 @@ Solver::Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int dev
     peer_base_[first_rank + l] = base;
   }
   PB_CUDA_CHECK(cudaMalloc(&dctx_, sizeof(RankCtx) * nlocal));
-  PB_CUDA_CHECK(cudaMalloc(&dmaps_, tensor_map_bytes() * 2 * kMapsPerVariant * nlocal));
+  PB_CUDA_CHECK(cudaMalloc(&dmaps_, tensor_map_bytes() * kMapVariants * kMapsPerVariant * nlocal));
   PB_CUDA_CHECK(cudaMallocHost(&pinned_opts_, sizeof(DeviceOptions)));
   PB_CUDA_CHECK(cudaMallocHost(&pinned_ctl_, sizeof(Control) * nlocal));
   for (auto& e : ev_) PB_CUDA_CHECK(cudaEventCreate(&e));
@@ -65,7 +65,7 @@ Solver::~Solver() {
   for (auto& e : ev_) cudaEventDestroy(e);
 }
 
-const void* Solver::host_maps(int l) const { return hmaps_ + (size_t)l * 2 * kMapsPerVariant * tensor_map_bytes(); }
+const void* Solver::host_maps(int l) const { return hmaps_ + (size_t)l * kMapVariants * kMapsPerVariant * tensor_map_bytes(); }
 
 double* Solver::array(int l, int which) const {
   if (which < 0 || which > 7) throw std::runtime_error("Solver::array: bad index");
@@ -142,18 +142,19 @@ void Solver::finalize() {
     c.sys_scope = nlocal() != nranks() ? 1 : 0;
     c.tiles_x = (b.nx + kTileX - 1) / kTileX;
     c.tiles_y = (b.ny + kTileY - 1) / kTileY;
-    c.tmaps = dmaps_ + (size_t)l * 2 * kMapsPerVariant * tensor_map_bytes();
+    c.tmaps = dmaps_ + (size_t)l * kMapVariants * kMapsPerVariant * tensor_map_bytes();
     hctx_.push_back(c);
   }
   // tensor maps for both tile heights (host-encoded, copied once)
-  hmaps_store_.assign(tensor_map_bytes() * 2 * kMapsPerVariant * nlocal() + 64, 0);
+  hmaps_store_.assign(tensor_map_bytes() * kMapVariants * kMapsPerVariant * nlocal() + 64, 0);
   char* hm = hmaps_ = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(hmaps_store_.data()) + 63) & ~uintptr_t(63));
   for (int l = 0; l < nlocal(); ++l) {
-    char* dst = hm + (size_t)l * 2 * kMapsPerVariant * tensor_map_bytes();
-    if (!build_tensor_maps(hctx_[l], 32, dst) || !build_tensor_maps(hctx_[l], 16, dst + kMapsPerVariant * tensor_map_bytes()))
+    char* dst = hm + (size_t)l * kMapVariants * kMapsPerVariant * tensor_map_bytes();
+    if (!build_tensor_maps(hctx_[l], 32, dst) || !build_tensor_maps(hctx_[l], 16, dst + kMapsPerVariant * tensor_map_bytes()) ||
+        !build_tensor_maps(hctx_[l], 64, dst + 2 * kMapsPerVariant * tensor_map_bytes()))
       throw std::runtime_error("cuTensorMapEncodeTiled failed");
   }
-  PB_CUDA_CHECK(cudaMemcpy(dmaps_, hm, tensor_map_bytes() * 2 * kMapsPerVariant * nlocal(), cudaMemcpyHostToDevice));
+  PB_CUDA_CHECK(cudaMemcpy(dmaps_, hm, tensor_map_bytes() * kMapVariants * kMapsPerVariant * nlocal(), cudaMemcpyHostToDevice));
   PB_CUDA_CHECK(cudaMemcpy(dctx_, hctx_.data(), sizeof(RankCtx) * nlocal(), cudaMemcpyHostToDevice));
   finalized_ = true;
 }

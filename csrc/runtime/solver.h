@@ -27,7 +27,7 @@ struct SolveOptions {
   int compressed = 1;       // TMA kernel: coefficient classes (1 byte/cell) instead of streaming a, b, D
   int ap_mode = 0;          // TMA kernel, uniform tiles: 1 store + reload Ap, 2 recompute it in phase C, 0 = default
   int l2_hints = 0;         // TMA loads carry L2 eviction priorities (helps ~2 % when the working set ~ L2 size)
-  int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages) or 16 (4 stages); 0 = auto
+  int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages), 16 (4 stages), 64 (32 + tall items); 0 = auto
   double watchdog_s = 0.0;  // 0 = default (20 s)
 };
 
@@ -77,6 +77,7 @@ class Solver {
   void gather_block(int l, double* dev_out, long long ld, cudaStream_t stream);
 
   int last_ctas_per_rank() const { return last_ctas_per_rank_; }
+  int last_tile_rows() const { return last_tile_rows_; }  // tile height the last persistent TMA solve ran with
   long long last_launches() const { return last_launches_; }
   int cta_report(int l, double* host_out, int max_ctas);  // the raw kCtaTimeWords doubles per CTA
   // tiles of the last persistent TMA solve by traffic class, summed over the local ranks: constant coefficients
@@ -111,6 +112,7 @@ class Solver {
   int sm_count_ = 148;
   int l2_bytes_ = 126 << 20;
   int last_ctas_per_rank_ = 0;
+  int last_tile_rows_ = 0;
   int last_method_ = 0;
   long long last_launches_ = 0;
 };

@@ -39,10 +39,25 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
     PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
     PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));
   }
-  if (tma)
-    PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, opt.tile_rows == 16 ? 16 : 32, exact,
-                                        opt.l2_hints, opt.compressed != 0, ap_recompute(opt.ap_mode), stream));
-  else
+  if (tma) {
+    // Tile height: 16 and 32 as asked; 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into
+    // tall items, which halves the fixed cost per tile of a phase.  Auto (0) takes 64 when Ap is recomputed (the
+    // tall phase-C stage has no room for stored p and Ap boxes) and every CTA still gets at least eight 64-row
+    // super-tiles (coarser work units balance worse: 800 x 1200 would leave CTAs with 2 against 1), else 32.
+    const bool recompute = ap_recompute(opt.ap_mode) && opt.compressed != 0;
+    long long super = 0;
+    for (const RankCtx& c : hctx_) super = std::max<long long>(super, (long long)((c.nx + 63) / 64) * ((c.ny + kTileY - 1) / kTileY));
+    int tile_rows = opt.tile_rows == 16 ? 16 : (opt.tile_rows == 64 ? 64 : 32);
+    if (opt.tile_rows == 0 && recompute && super >= 8LL * ctas) tile_rows = 64;
+    if (tile_rows == 64 && !recompute) tile_rows = 32;
+    const long long per_cta = (max_tiles * (tile_rows == 16 ? 2 : 1) + ctas - 1) / ctas;
+    if (per_cta > persistent_tma_max_items())
+      throw std::runtime_error("block too large for one GPU: " + std::to_string(per_cta) + " tiles per CTA, the persistent "
+                               "kernel holds " + std::to_string(persistent_tma_max_items()) + "; use more GPUs");
+    last_tile_rows_ = tile_rows;
+    PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, tile_rows, exact, opt.l2_hints, opt.compressed != 0,
+                                        ap_recompute(opt.ap_mode), stream));
+  } else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;
 }

@@ -130,7 +130,9 @@ typedef struct pb_solve_options {
                          1, three instructions), 0 multiplication by the reciprocal (last-bit differences) */
   int ctas_per_sm;    /* 0 = auto */
   int error_report;   /* 1: compute the error against the analytic solution after the solve */
-  int tile_rows;      /* TMA persistent kernel: 32 (2 pipeline stages) or 16 (4 stages); 0 = auto */
+  int tile_rows;      /* TMA persistent kernel: 32 (2 pipeline stages), 16 (4 stages), 64 (32-row tiles with pairs of full
+                         constant-coefficient tiles merged into 64-row items; needs the recomputed Ap, else 32 is
+                         used); 0 = auto */
   double watchdog_s;  /* 0 = default (20 s): device-side waits give up after this long */
   int l2_hints;       /* 1: TMA loads carry L2 eviction priorities (keep r, D, p; stream a, b, w, Ap) */
   int full_coefficients; /* 1: stream a, b, D as fp64 boxes instead of the 1-byte coefficient classes (A/B testing) */

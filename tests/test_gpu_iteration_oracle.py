@@ -78,7 +78,7 @@ def _close(got, ref, what):
 
 @pytest.mark.parametrize("iters", [1, 2])
 @pytest.mark.parametrize("pg", [(1, 1), (2, 2)])
-@pytest.mark.parametrize("tile_rows,ap_mode", [(32, 1), (32, 2), (16, 1)])
+@pytest.mark.parametrize("tile_rows,ap_mode", [(32, 1), (32, 2), (16, 1), (64, 2)])
 def test_first_iterations_against_pytorch(iters, pg, tile_rows, ap_mode):
     M, N = 400, 600
     w_ref, r_ref, p_ref, Ap_ref = _torch_pcg(M, N, iters)
@@ -97,7 +97,7 @@ def test_first_iterations_against_pytorch(iters, pg, tile_rows, ap_mode):
     s.close()
 
 
-@pytest.mark.parametrize("tile_rows", [32, 16])
+@pytest.mark.parametrize("tile_rows", [32, 16, 64])
 @pytest.mark.parametrize("ap_mode", [1, 2])
 def test_converged_solution_elementwise_against_cpu_oracle(native, tile_rows, ap_mode):
     M, N = 400, 600
@@ -112,6 +112,24 @@ def test_converged_solution_elementwise_against_cpu_oracle(native, tile_rows, ap
         w = s.solution_host()
         assert float((w - ref).abs().max()) < 1e-10
         s.close()
+
+
+def test_tall_items_are_used_and_counted():
+    """tile_rows=64 merges pairs of full constant-coefficient tiles; the kernel's own tile counts must still add up to
+    the number of 32 x 64 tiles of the block, and the result must agree with 32-row tiles to rounding."""
+    M, N = 1600, 1200
+    s = _solver(M, N)
+    ra = s.solve(tile_rows=32, ap_mode=2)
+    ta = s.tile_counts()
+    wa = s.solution_host().clone()
+    rb = s.solve(tile_rows=64, ap_mode=2)
+    tb = s.tile_counts()
+    wb = s.solution_host()
+    ntiles = ((M - 1 + 31) // 32) * ((N - 1 + 63) // 64)
+    assert sum(ta.values()) == ntiles == sum(tb.values())
+    assert ra["iters"] == rb["iters"]
+    assert float((wa - wb).abs().max()) < 1e-11
+    s.close()
 
 
 def test_headline_grid_50_iterations_against_step_kernels():
