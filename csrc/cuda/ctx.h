@@ -34,6 +34,8 @@ constexpr size_t kCtaTimesOffset = 81920;          // [kMaxCtas][kCtaTimeWords] 
                                                    // tiles by kind (constant coefficients with Ap recomputed / stored, mixed), ns halo wait
 constexpr size_t kLl1Offset = 147456;              // [kRedValues][kMaxCtas][2] u64: per-CTA records of star_sum (CTA -> CTA 0)
 constexpr size_t kResOffset = 180224;              // [kRedValues][2] u64: result record of star_sum (CTA 0 -> every CTA)
+constexpr size_t kTileCodeOffset = 180352;         // one code byte per super-tile (TMA kernel, cost-balanced tile assignment)
+constexpr int kTileCodeBytes = 16256;              // up to the end of the header
 #ifdef PB_VAR_HDR  // experiment only: the round-1 position of the arrays (star_sum's areas then overlap the first array)
 constexpr size_t kHeaderBytes = 131072;
 #else

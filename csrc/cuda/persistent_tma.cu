@@ -90,7 +90,7 @@ struct TmaCfg {
 template <int TX, int DIV, bool CC>
 __global__ void __launch_bounds__(kThreads, 1)
 pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints,
-                          int recompute_ap, int tall_mode) {
+                          int recompute_ap, int tall_mode, int balance_mode) {
   using Cfg = TmaCfg<TX>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
@@ -173,8 +173,16 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // "outside" (1/eps, diag_out), 2 = mixed (full coefficient boxes).  Full tiles with constant coefficients can get Ap
   // in phase C by evaluating the stencil again on the p_new box (the same device function on the same operands: the
   // same bits), which saves the store and the reload of Ap.
+  // Which CTA works on which super-tile.  Cyclic (t mod ncta) when every tile costs the same; but tall items are
+  // cheaper per node than 32-row items and mixed tiles dearer, and the CTAs that get the ellipse's boundary end up
+  // 10 % behind the others, who then wait for them in both reductions (measured at 4096^2: 27 us of a 215 us
+  // iteration).  So: every CTA classifies its cyclic share and publishes one code byte per super-tile, one grid-wide
+  // barrier, then warp 0 of every CTA walks the super-tiles in sweep order and gives each to the CTA with the least
+  // cost so far (ties: lowest CTA).  Same integers everywhere, so every CTA arrives at the same assignment; with equal
+  // costs it is the cyclic one; the sweep order -- and with it the "edge rows first" order of the halo -- is kept.
   int nmine = 0;  // items; uniform across the CTA
   {
+    __shared__ int s_nmine;
     auto classify = [&](int li0, int lj0, int cx, int cy) -> int {
       if constexpr (!CC) return 2;
       bool all_in = true, all_out = true;
@@ -188,15 +196,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const int in = __syncthreads_and(all_in ? 1 : 0), out = __syncthreads_and(all_out ? 1 : 0);
       return in ? 0 : (out ? 1 : 2);
     };
-    auto add_item = [&](int li0, int lj0, int flags) {
-      if (threadIdx.x == 0 && nmine < kMaxItems) {
-        s_items[nmine].li0 = (unsigned short)li0, s_items[nmine].lj0 = (unsigned short)lj0;
-        s_items[nmine].flags = (unsigned char)flags, s_items[nmine].pad = 0;
-      }
-      ++nmine;
-    };
-    for (int j = 0; j < nsuper; ++j) {
-      const int t = cta + j * ncta;
+    auto origin = [&](int t, int& li0, int& lj0) {
       int tx = t / tiles_y;
       const int ty = t - tx * tiles_y;
       // Row order: first, last, second, ...: the tiles that store halo rows for the x-neighbours (phase C) and the
@@ -204,7 +204,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       // halo records hides behind the remaining tiles instead of sitting in front of a reduction.  (Enumerating the
       // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
       if (has_nbr && tiles_x > 2) tx = tx == 0 ? 0 : (tx == 1 ? tiles_x - 1 : tx - 1);
-      const int li0 = 1 + tx * srows, lj0 = 1 + ty * TY;
+      li0 = 1 + tx * srows, lj0 = 1 + ty * TY;
+    };
+    // code of a super-tile: bits 0-1 class of the first half, 2-3 of the second, 4 second half exists, 5 tall,
+    // 6 / 7 first / second half is a full tile
+    auto super_code = [&](int li0, int lj0) -> int {
       const int cy = min(TY, c.ny - lj0 + 1);
       const int cx0 = min(TX, c.nx - li0 + 1);
       const int m0 = classify(li0, lj0, cx0, cy);
@@ -215,12 +219,81 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         cx1 = min(TX, c.nx - (li0 + TX) + 1);
         m1 = classify(li0 + TX, lj0, cx1, cy);
       }
-      if (second && full0 && cx1 == TX && m0 != 2 && m0 == m1) {
-        add_item(li0, lj0, m0 | kItemRecomp | kItemTall);
-      } else {
-        add_item(li0, lj0, m0 | ((recompute_ap && m0 != 2 && full0) ? kItemRecomp : 0));
-        if (second) add_item(li0 + TX, lj0, m1 | ((recompute_ap && m1 != 2 && cx1 == TX && cy == TY) ? kItemRecomp : 0));
+      const bool full1 = second && cx1 == TX && cy == TY;
+      const bool tall = second && full0 && full1 && m0 != 2 && m0 == m1;
+      return m0 | (m1 << 2) | (second ? 16 : 0) | (tall ? 32 : 0) | (full0 ? 64 : 0) | (full1 ? 128 : 0);
+    };
+    // items of a super-tile, appended by `writer` (one thread); returns how many
+    auto emit = [&](int li0, int lj0, int code, int at, bool writer) -> int {
+      const int m0 = code & 3, m1 = (code >> 2) & 3;
+      auto put = [&](int k, int li, int flags) {
+        if (writer && k < kMaxItems) {
+          s_items[k].li0 = (unsigned short)li, s_items[k].lj0 = (unsigned short)lj0;
+          s_items[k].flags = (unsigned char)flags, s_items[k].pad = 0;
+        }
+      };
+      if (code & 32) {
+        put(at, li0, m0 | kItemRecomp | kItemTall);
+        return 1;
       }
+      put(at, li0, m0 | ((recompute_ap && m0 != 2 && (code & 64)) ? kItemRecomp : 0));
+      if (!(code & 16)) return 1;
+      put(at + 1, li0 + TX, m1 | ((recompute_ap && m1 != 2 && (code & 128)) ? kItemRecomp : 0));
+      return 2;
+    };
+    // relative cost of a super-tile, phases AB + C, in 0.1 us (measured: tall item 6.8 us, 32-row item with constant
+    // coefficients 3.8 us, mixed 4.5 us)
+    auto cost = [&](int code) -> int {
+      if (code & 32) return 68;
+      return ((code & 3) == 2 ? 45 : 38) + ((code & 16) ? (((code >> 2) & 3) == 2 ? 45 : 38) : 0);
+    };
+    unsigned char* tcode = reinterpret_cast<unsigned char*>(ctl) + kTileCodeOffset;
+    const bool balance = CC && balance_mode != 0 && ncta > 1 && ntiles <= kTileCodeBytes;
+    for (int j = 0; j < nsuper; ++j) {
+      const int t = cta + j * ncta;
+      int li0, lj0;
+      origin(t, li0, lj0);
+      const int code = super_code(li0, lj0);
+      if (balance) {
+        if (threadIdx.x == 0) tcode[t] = (unsigned char)code;
+      } else {
+        nmine += emit(li0, lj0, code, nmine, threadIdx.x == 0);
+      }
+    }
+    if (balance) {
+      {  // grid-wide barrier (a reduction of nothing): everybody's codes are written and released
+        double v[1] = {0.0};
+        ++seq;
+        PB_RED_PRE
+        (void)PB_RED(1);
+      }
+      if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        int* load = reinterpret_cast<int*>(s_dyn);  // the stage memory is free until the first load is issued
+        for (int i = lane; i < ncta; i += 32) load[i] = 0;
+        __syncwarp();
+        int mine = 0;
+        int chunk = 0;  // codes of super-tiles t0 .. t0 + 31, one per lane
+        for (int t = 0; t < ntiles; ++t) {
+          if ((t & 31) == 0) chunk = t + lane < ntiles ? (int)__ldcg(tcode + t + lane) : 0;
+          const int code = __shfl_sync(0xffffffffu, chunk, t & 31);
+          int best = 0x7fffffff;  // key = cost so far * 1024 + CTA: the minimum is unique
+          for (int i = lane; i < ncta; i += 32) best = min(best, load[i] * 1024 + i);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+          const int who = best & 1023;
+          if (lane == 0) load[who] += cost(code);
+          if (who == cta) {
+            int li0, lj0;
+            origin(t, li0, lj0);
+            mine += emit(li0, lj0, code, mine, lane == 0);
+          }
+          __syncwarp();
+        }
+        if (lane == 0) s_nmine = mine;
+      }
+      __syncthreads();
+      nmine = s_nmine;
     }
     nmine = min(nmine, kMaxItems);  // the host sizes the launch so that this never cuts anything off
     __syncthreads();
@@ -816,36 +889,37 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 // ---------------------------------------------------------------------------------------------------
 template <int TX, int DIV, bool CC>
 static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int l2_hints,
-                                  int recompute_ap, int tall, cudaStream_t stream) {
+                                  int recompute_ap, int tall, int balance, cudaStream_t stream) {
   const void* fn = (const void*)pcg_persistent_tma_kernel<TX, DIV, CC>;
   const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints, (void*)&recompute_ap, (void*)&tall};
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints, (void*)&recompute_ap, (void*)&tall,
+                  (void*)&balance};
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
 }
 
 template <int TX, bool CC>
 static cudaError_t launch_div(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int variant, int div, int l2_hints,
-                              int recompute_ap, int tall, cudaStream_t stream) {
+                              int recompute_ap, int tall, int balance, cudaStream_t stream) {
   if (div == kDivTrue)
-    return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, stream);
+    return launch_variant<TX, kDivTrue, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, balance, stream);
   if (div == kDivMarkstein)
-    return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, stream);
-  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, stream);
+    return launch_variant<TX, kDivMarkstein, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, balance, stream);
+  return launch_variant<TX, kDivRecip, CC>(d_ctxs, nvirt, ctas_per_rank, variant, l2_hints, recompute_ap, tall, balance, stream);
 }
 
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
-                                  int l2_hints, bool compressed, bool recompute_ap, cudaStream_t stream) {
-  const int ra = (compressed && recompute_ap) ? 1 : 0;  // without coefficient classes no tile is known to be constant
+                                  int l2_hints, bool compressed, bool recompute_ap, bool balance, cudaStream_t stream) {
+  const int ra = (compressed && recompute_ap) ? 1 : 0, bal = balance ? 1 : 0;  // without coefficient classes no tile is known to be constant
   // tile_rows: 16, 32, or 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into tall items
   // (needs the recomputed Ap: a tall phase-C stage has no room for p and Ap boxes)
   if (tile_rows == 16)
-    return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, stream)
-                      : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, stream);
+    return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, bal, stream)
+                      : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, 0, stream);
   const int tall = (tile_rows == 64 && ra) ? 1 : 0;
-  return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, tall, stream)
-                    : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, 0, stream);
+  return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, tall, bal, stream)
+                    : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, 0, 0, stream);
 }
 
 int persistent_tma_max_items() { return kMaxItems; }

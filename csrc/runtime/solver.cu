@@ -21,7 +21,8 @@ static_assert(kPartialsOffset + kMaxCtas * kPartialStride * 8 <= kCtaTimesOffset
 #ifndef PB_VAR_HDR
 static_assert(kCtaTimesOffset + kMaxCtas * kCtaTimeWords * 8 <= kLl1Offset, "per-CTA report area overflows");
 static_assert(kLl1Offset + kRedValues * kMaxCtas * 16 <= kResOffset, "star_sum CTA records overflow");
-static_assert(kResOffset + kRedValues * 16 <= kHeaderBytes, "star_sum result record overflows");
+static_assert(kResOffset + kRedValues * 16 <= kTileCodeOffset, "star_sum result record overflows");
+static_assert(kTileCodeOffset + kTileCodeBytes <= kHeaderBytes, "tile codes overflow");
 #endif
 static_assert(kHeaderBytes % 4096 == 0, "arrays must start page-aligned (TMA base alignment)");
 

@@ -1,6 +1,7 @@
 // solver_run.cu -- Solver::solve and friends (the part of solver.h that enqueues work).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -55,8 +56,9 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
       throw std::runtime_error("block too large for one GPU: " + std::to_string(per_cta) + " tiles per CTA, the persistent "
                                "kernel holds " + std::to_string(persistent_tma_max_items()) + "; use more GPUs");
     last_tile_rows_ = tile_rows;
+    static const bool no_balance = std::getenv("PB_NO_BALANCE") != nullptr;  // A/B switch for measurements
     PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, tile_rows, exact, opt.l2_hints, opt.compressed != 0,
-                                        ap_recompute(opt.ap_mode), stream));
+                                        ap_recompute(opt.ap_mode), !no_balance, stream));
   } else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;
