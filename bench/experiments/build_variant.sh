@@ -8,7 +8,7 @@ NAME=$1; shift
 ROOT=$(cd "$(dirname "$0")/../.." && pwd)
 OUT=$ROOT/build/variants/$NAME
 mkdir -p "$OUT"
-SRCS="core/decomp.cpp cpu/oracle.cpp cpu/dist_solver.cpp runtime/shm_comm.cpp api/c_api_cpu.cpp cuda/assemble.cu cuda/step_kernels.cu cuda/persistent.cu cuda/persistent_tma.cu cuda/apply_a_op.cu runtime/solver.cu runtime/solver_run.cu runtime/group.cu api/c_api_cuda.cu"
+SRCS="core/decomp.cpp cpu/oracle.cpp cpu/dist_solver.cpp runtime/shm_comm.cpp api/c_api_cpu.cpp cuda/assemble.cu cuda/step_kernels.cu cuda/persistent.cu cuda/persistent_tma.cu cuda/resident.cu cuda/apply_a_op.cu runtime/solver.cu runtime/solver_run.cu runtime/group.cu api/c_api_cuda.cu"
 pids=()
 for s in $SRCS; do
   o=$OUT/$(echo $s | tr / _).o

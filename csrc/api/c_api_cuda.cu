@@ -139,6 +139,7 @@ int pb_solver_cta_report(pb_solver* s, int local_idx, double* host_out, int max_
   const int rc = guarded([&] { n = s->impl.cta_report(local_idx, host_out, max_ctas); });
   return rc != 0 ? rc : n;
 }
+const char* pb_solver_last_kernel(pb_solver* s) { return s->impl.last_kernel(); }
 int pb_solver_tile_counts(pb_solver* s, long long* out3) {
   return guarded([&] { s->impl.tile_counts(out3); });
 }

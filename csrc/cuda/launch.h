@@ -33,6 +33,14 @@ cudaError_t launch_tma_probe(const void* dmaps, const void* hmaps, int idx, int 
 bool build_tensor_maps(const RankCtx& h_ctx, int tile_rows, void* out12);
 size_t tensor_map_bytes();
 
+// KR (resident.cu): blocks that fit into the SMs' shared memory, one sub-block per CTA
+struct ResidentCut {
+  int sx, sy_log2, bx, by;  // sub-block rows, log2 of its columns, sub-blocks along x and y (bx * by CTAs per rank)
+};
+bool resident_partition(int nx, int ny, int max_ctas, size_t max_smem_bytes, ResidentCut* out);
+size_t resident_smem_bytes(const ResidentCut& cut);
+cudaError_t launch_resident(const RankCtx* d_ctxs, int nvirt, const ResidentCut& cut, int div, cudaStream_t stream);
+
 // step-wise kernels (step_kernels.cu); every kernel returns immediately when Control::status is not
 // PB_STATUS_RUNNING, so the host may enqueue iterations ahead of the stop test.
 enum StepPhase : int { kStepInit = 0, kStepAlpha = 1, kStepBeta = 2 };

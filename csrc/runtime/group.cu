@@ -124,7 +124,8 @@ DeviceGroup::~DeviceGroup() {
 }
 
 void DeviceGroup::solve(const SolveOptions& opt, pb_stats* out) {
-  if (opt.method != kMethodPersistent && opt.method != kMethodPersistentLdg && solvers_.size() > 1)
+  if (opt.method != kMethodPersistent && opt.method != kMethodPersistentLdg && opt.method != kMethodResident &&
+      opt.method != kMethodPersistentTma && solvers_.size() > 1)
     throw std::runtime_error("DeviceGroup: only the persistent method runs on several devices");
   double t_prev = trace_now();
   for (size_t r = 0; r < solvers_.size(); ++r) solvers_[r]->enqueue(opt, streams_[r]);

@@ -11,10 +11,18 @@
 
 #include "../../include/poisson_b200.h"
 #include "../cuda/ctx.h"
+#include "../cuda/launch.h"
 
 namespace pb {
 
-enum Method : int { kMethodPersistent = 0, kMethodStepFused = 1, kMethodStepClassic = 2, kMethodPersistentLdg = 3 };
+enum Method : int {
+  kMethodPersistent = 0,     // TMA kernel; blocks that fit on chip go to the resident kernel unless options pin the TMA one
+  kMethodStepFused = 1,
+  kMethodStepClassic = 2,
+  kMethodPersistentLdg = 3,
+  kMethodResident = 4,       // shared-memory-resident kernel (refused when the block does not fit)
+  kMethodPersistentTma = 5   // TMA kernel, never the resident one
+};
 
 struct SolveOptions {
   int method = kMethodPersistent;
@@ -78,6 +86,7 @@ class Solver {
 
   int last_ctas_per_rank() const { return last_ctas_per_rank_; }
   int last_tile_rows() const { return last_tile_rows_; }  // tile height the last persistent TMA solve ran with
+  const char* last_kernel() const { return last_kernel_; }
   long long last_launches() const { return last_launches_; }
   int cta_report(int l, double* host_out, int max_ctas);  // the raw kCtaTimeWords doubles per CTA
   // tiles of the last persistent TMA solve by traffic class, summed over the local ranks: constant coefficients
@@ -90,6 +99,7 @@ class Solver {
 
  private:
   void solve_persistent(const SolveOptions& opt, cudaStream_t stream);
+  bool resident_cut(ResidentCut* cut) const;  // the cut of the local blocks into one sub-block per CTA, if they fit
   void solve_steps(const SolveOptions& opt, cudaStream_t stream);
 
   Grid grid_;
@@ -113,6 +123,7 @@ class Solver {
   int l2_bytes_ = 126 << 20;
   int last_ctas_per_rank_ = 0;
   int last_tile_rows_ = 0;
+  const char* last_kernel_ = "";  // "tma", "ldg" or "resident": what the last persistent solve ran
   int last_method_ = 0;
   long long last_launches_ = 0;
 };

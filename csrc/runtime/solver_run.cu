@@ -22,10 +22,38 @@ bool Solver::ap_recompute(int ap_mode) const {
   return touched > (size_t)l2_bytes_ / 5 * 4;
 }
 
+bool Solver::resident_cut(ResidentCut* cut) const {
+  // one cut for all ranks of the solve (every rank must take the same decision, and one launch serves all local
+  // ranks): sized for the largest block of the whole grid, which is block 0
+  const LocalBlock b0 = make_local_block(grid_.M, grid_.N, pg_, 0);
+  const int nx = b0.nx, ny = b0.ny;
+  return resident_partition(nx, ny, std::min(sm_count_ / nlocal(), kMaxCtas), (size_t)(227 - 10) * 1024, cut);
+}
+
 void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   if (!fabric_complete_) throw std::runtime_error("persistent solve needs every rank's arena (open_peer) first");
   const int exact = opt.exact_div;
-  const bool tma = opt.method == kMethodPersistent;
+  // Blocks that fit into the SMs' shared memory run in the resident kernel: no field data moves through L2 / HBM
+  // during the iteration.  Options that only exist for the TMA kernel (tile height, Ap mode, streamed coefficients,
+  // L2 hints) pin that kernel, as does method = persistent_tma.
+  ResidentCut cut{};
+  const bool want_resident = opt.method == kMethodResident ||
+                             (opt.method == kMethodPersistent && opt.tile_rows == 0 && opt.ap_mode == 0 &&
+                              opt.compressed != 0 && opt.l2_hints == 0 && std::getenv("PB_NO_RESIDENT") == nullptr);
+  if (want_resident && resident_cut(&cut)) {
+    for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));
+    last_ctas_per_rank_ = cut.bx * cut.by;
+    last_tile_rows_ = 0;
+    last_kernel_ = "resident";
+    PB_CUDA_CHECK(launch_resident(dctx_, nlocal(), cut, exact, stream));
+    last_launches_ += 1;
+    return;
+  }
+  if (opt.method == kMethodResident)
+    throw std::runtime_error("method 'resident': the block does not fit into the shared memory of the SMs (at most 8192 "
+                             "nodes per CTA); use method 'persistent'");
+  const bool tma = opt.method != kMethodPersistentLdg;
+  last_kernel_ = tma ? "tma" : "ldg";
   int per_sm = tma ? 1 : persistent_max_ctas_per_sm(exact);
   if (per_sm < 1) throw std::runtime_error("persistent kernel does not fit on an SM");
   if (!tma && opt.ctas_per_sm > 0) per_sm = std::min(per_sm, opt.ctas_per_sm);
@@ -120,7 +148,8 @@ void Solver::enqueue(const SolveOptions& opt, cudaStream_t stream) {
   for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(launch_assemble(dctx_ + l, hctx_[l], stream));
   last_launches_ += nlocal();
   PB_CUDA_CHECK(cudaEventRecord(ev_[1], stream));
-  if (opt.method == kMethodPersistent || opt.method == kMethodPersistentLdg)
+  if (opt.method == kMethodPersistent || opt.method == kMethodPersistentLdg || opt.method == kMethodResident ||
+      opt.method == kMethodPersistentTma)
     solve_persistent(opt, stream);
   else
     solve_steps(opt, stream);
@@ -168,7 +197,8 @@ void Solver::collect(cudaStream_t stream, pb_stats* out) {
   out->seconds = 1e-3 * (double)(ms_asm + ms_iter + ms_err);
   out->t_assemble = 1e-3 * ms_asm;
   out->t_iterations = 1e-3 * ms_iter;
-  if (last_method_ == kMethodPersistent || last_method_ == kMethodPersistentLdg) {
+  if (last_method_ == kMethodPersistent || last_method_ == kMethodPersistentLdg || last_method_ == kMethodResident ||
+      last_method_ == kMethodPersistentTma) {
     // The reference's five buckets (S4:695-700), fed from CTA 0's device clocks; every nanosecond of the loop is in
     // exactly one of them.  gpu = the two phases minus the halo wait inside them; comm = waiting for and unpacking
     // the neighbours' halo records (TMA kernel; the plain-load kernel publishes its halo inside reduction 2, so its
@@ -229,7 +259,7 @@ void Solver::tile_counts(long long out[3]) {
   PB_CUDA_CHECK(cudaSetDevice(device_));
   out[0] = out[1] = out[2] = 0;
   const int n = last_ctas_per_rank_;
-  if (n <= 0 || last_method_ != kMethodPersistent) return;
+  if (n <= 0 || std::string(last_kernel_) != "tma") return;
   std::vector<double> buf((size_t)n * kCtaTimeWords);
   for (int l = 0; l < nlocal(); ++l) {
     PB_CUDA_CHECK(cudaMemcpy(buf.data(), arenas_[l] + kCtaTimesOffset, sizeof(double) * buf.size(), cudaMemcpyDeviceToHost));

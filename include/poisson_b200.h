@@ -116,10 +116,15 @@ int pb_cpu_error_local(int M, int N, const pb_block* blk, const double* w, doubl
  * Single-GPU "virtual ranks": nlocal = Px*Py, no exchange needed. */
 typedef struct pb_solver pb_solver;
 
-#define PB_METHOD_PERSISTENT 0   /* one cooperative launch per solve, fused halo + reductions */
+#define PB_METHOD_PERSISTENT 0   /* one cooperative launch per solve, fused halo + reductions: the resident kernel for blocks
+                                    that fit on chip (unless tile_rows / ap_mode / l2_hints / full_coefficients are set),
+                                    else the TMA kernel */
 #define PB_METHOD_STEP_FUSED 1   /* separate launches, fused p-update + stencil (single rank) */
 #define PB_METHOD_STEP_CLASSIC 2 /* separate launches, reference-like 3-kernel structure (single rank) */
 #define PB_METHOD_PERSISTENT_LDG 3 /* persistent kernel with plain global loads instead of TMA pipelines */
+#define PB_METHOD_RESIDENT 4       /* persistent kernel that keeps p, r, w of a small block in shared memory for the whole
+                                      solve (<= 8192 nodes per CTA, i.e. ~1.2 M nodes per GPU); an error when it does not fit */
+#define PB_METHOD_PERSISTENT_TMA 5 /* the TMA kernel even where PB_METHOD_PERSISTENT would take the resident one */
 
 typedef struct pb_solve_options {
   int method;
@@ -172,6 +177,8 @@ int pb_solver_cta_times(pb_solver* s, int local_idx, double* host_out, int max_c
    counts below, ns waiting for halo records; after pb_solver_xgpu_bench mode 5: mean clock cycles per step of the
    reduction).  Returns the number of CTAs written or < 0. */
 int pb_solver_cta_report(pb_solver* s, int local_idx, double* host_out, int max_ctas);
+/* Which kernel the last persistent solve ran: "resident", "tma" or "ldg" ("" before the first solve). */
+const char* pb_solver_last_kernel(pb_solver* s);
 /* Tiles of the last persistent (TMA) solve by what they move per node and iteration, summed over the local ranks:
    out3 = {constant coefficients with Ap recomputed (64 B), constant coefficients with Ap stored (80 B), mixed tiles
    that stream a, b, D (112 B)}.  Counted by the kernel itself; the benchmark's roofline uses these. */

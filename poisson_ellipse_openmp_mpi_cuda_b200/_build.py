@@ -37,6 +37,7 @@ LIB_SOURCES = [
     "cuda/step_kernels.cu",
     "cuda/persistent.cu",
     "cuda/persistent_tma.cu",
+    "cuda/resident.cu",
     "cuda/apply_a_op.cu",
     "runtime/solver.cu",
     "runtime/solver_run.cu",

@@ -135,6 +135,7 @@ def _declare(lib: C.CDLL) -> None:
         "pb_solver_cta_times": (I, [vp, I, dp, I]),
         "pb_solver_cta_report": (I, [vp, I, dp, I]),
         "pb_solver_tile_counts": (I, [vp, C.POINTER(LL)]),
+        "pb_solver_last_kernel": (C.c_char_p, [vp]),
         "pb_group_create": (vp, [I, I, I, I, C.POINTER(I), I]),
         "pb_group_destroy": (None, [vp]),
         "pb_group_solve": (I, [vp, C.POINTER(SolveOptions), C.POINTER(Stats)]),

@@ -14,7 +14,7 @@ from . import _native
 
 NORMS = {"weighted": 0, "unweighted": 1}
 DIVS = {"recip": 0, "true": 1, "markstein": 2}
-METHODS = {"persistent": 0, "step_fused": 1, "step_classic": 2, "persistent_ldg": 3}
+METHODS = {"persistent": 0, "step_fused": 1, "step_classic": 2, "persistent_ldg": 3, "resident": 4, "persistent_tma": 5}
 STATUS = {0: "max_iter", 1: "converged", 2: "breakdown", 3: "running", 4: "watchdog", 5: "tma_timeout"}
 ARRAYS = {"w": 0, "r": 1, "p0": 2, "p1": 3, "Ap": 4, "a": 5, "b": 6, "D": 7}
 
@@ -176,6 +176,7 @@ class GpuSolver:
         out = st.as_dict()
         out["status_name"] = STATUS.get(st.status, "?")
         out.update(self.info())
+        out["kernel"] = (self.lib.pb_solver_last_kernel(self._h) or b"").decode()
         if st.status in (4, 5):
             raise RuntimeError(f"device-side {STATUS[st.status]}: the solve was abandoned (debug: {out})")
         return out

@@ -46,7 +46,7 @@ def test_assembly_bit_exact(native):
     s.close()
 
 
-@pytest.mark.parametrize("method", ["persistent", "persistent_ldg", "step_fused", "step_classic"])
+@pytest.mark.parametrize("method", ["persistent", "persistent_tma", "resident", "persistent_ldg", "step_fused", "step_classic"])
 @pytest.mark.parametrize("grid", [(10, 10), (40, 40), (160, 160), (400, 600)])
 def test_iteration_parity_single_rank(grid, method):
     s = _solver(*grid)
@@ -65,15 +65,17 @@ def test_unweighted_norm(grid):
     s.close()
 
 
+@pytest.mark.parametrize("method", ["persistent_tma", "resident"])
 @pytest.mark.parametrize("pg", [(1, 2), (2, 1), (2, 2), (2, 4), (3, 3)])
 @pytest.mark.parametrize("grid", [(40, 40), (160, 160), (400, 600)])
-def test_virtual_ranks_match_single(grid, pg):
+def test_virtual_ranks_match_single(grid, pg, method):
     """Px x Py virtual ranks on one GPU (one cooperative launch): same iterations, same solution."""
     one = _solver(*grid)
-    r1 = one.solve()
+    r1 = one.solve(method=method)
     w1 = one.solution_host()
     many = _solver(*grid, pg[0], pg[1])
-    rm = many.solve()
+    rm = many.solve(method=method)
+    assert rm["kernel"] == ("tma" if method == "persistent_tma" else "resident")
     wm = many.solution_host()
     assert rm["iters"] == r1["iters"] == ITERS_WEIGHTED[grid]
     assert torch.allclose(w1, wm, rtol=0, atol=1e-12)
@@ -147,11 +149,20 @@ def test_repeated_solves_and_max_iter():
     s.close()
 
 
-def test_large_grid_800x1200():
+@pytest.mark.parametrize("method,kernel", [("persistent", "resident"), ("persistent_tma", "tma")])
+def test_large_grid_800x1200(method, kernel):
     s = _solver(800, 1200)
-    res = s.solve()
-    assert res["iters"] == 989
+    res = s.solve(method=method)
+    assert res["iters"] == 989 and res["kernel"] == kernel
     _check_errors(res, (800, 1200))
+    s.close()
+
+
+def test_resident_kernel_is_refused_for_blocks_that_do_not_fit():
+    s = _solver(2048, 2048)
+    assert s.solve(max_iter=5)["kernel"] == "tma"  # auto: too large for shared memory
+    with pytest.raises(RuntimeError, match="does not fit"):
+        s.solve(method="resident", max_iter=5)
     s.close()
 
 
@@ -223,10 +234,11 @@ def test_recomputed_Ap_is_bit_identical_to_stored_Ap(pg, tile_rows):
         s.close()
 
 
-def test_per_cta_clocks():
+@pytest.mark.parametrize("method", ["persistent", "persistent_tma"])
+def test_per_cta_clocks(method):
     """Every CTA reports where it spent the solve; the four parts add up to (at most) the device time of the loop."""
     s = _solver(800, 1200)
-    r = s.solve()
+    r = s.solve(method=method)
     t = s.cta_times()
     assert tuple(t.shape) == (r["ctas_per_rank"], 4)
     assert (t >= 0).all() and t[:, :2].min() > 0
