@@ -90,6 +90,7 @@ int pb_solver_solve(pb_solver* s, const pb_solve_options* o, void* stream, pb_st
     opt.l2_hints = o->l2_hints;
     opt.compressed = o->full_coefficients ? 0 : 1;
     opt.ap_mode = o->ap_mode;
+    opt.no_balance = o->no_balance;
     opt.watchdog_s = o->watchdog_s;
     s->impl.solve(opt, as_stream(stream), stats);
   });
@@ -176,6 +177,7 @@ int pb_group_solve(pb_group* g, const pb_solve_options* o, pb_stats* stats) {
     opt.l2_hints = o->l2_hints;
     opt.compressed = o->full_coefficients ? 0 : 1;
     opt.ap_mode = o->ap_mode;
+    opt.no_balance = o->no_balance;
     opt.watchdog_s = o->watchdog_s;
     g->impl.solve(opt, stats);
   });

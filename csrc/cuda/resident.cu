@@ -327,7 +327,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
   if (threadIdx.x == 0) {
     double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(ctl) + kCtaTimesOffset) + kCtaTimeWords * cta;
     mine[0] = (double)t_ab, mine[1] = (double)t_c, mine[2] = (double)t_r1, mine[3] = (double)t_r2;
-    mine[4] = 0.0, mine[5] = 0.0, mine[6] = 0.0;
+    mine[4] = (double)mode, mine[5] = (double)(cx * cy), mine[6] = 0.0;  // (diagnostics: class and size of the sub-block)
     mine[7] = (double)t_halo;
   }
   __syncthreads();

@@ -84,9 +84,9 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
       throw std::runtime_error("block too large for one GPU: " + std::to_string(per_cta) + " tiles per CTA, the persistent "
                                "kernel holds " + std::to_string(persistent_tma_max_items()) + "; use more GPUs");
     last_tile_rows_ = tile_rows;
-    static const bool no_balance = std::getenv("PB_NO_BALANCE") != nullptr;  // A/B switch for measurements
+    static const bool env_no_balance = std::getenv("PB_NO_BALANCE") != nullptr;  // A/B switch for measurements
     PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, tile_rows, exact, opt.l2_hints, opt.compressed != 0,
-                                        ap_recompute(opt.ap_mode), !no_balance, stream));
+                                        ap_recompute(opt.ap_mode), !(env_no_balance || opt.no_balance), stream));
   } else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;
@@ -246,6 +246,7 @@ int Solver::cta_times(int l, double* host_out, int max_ctas) {
   return n;
 }
 
+// (after a resident-kernel solve words 4 and 5 hold the sub-block's coefficient class and node count instead)
 int Solver::cta_report(int l, double* host_out, int max_ctas) {
   PB_CUDA_CHECK(cudaSetDevice(device_));
   const int n = std::min(last_ctas_per_rank_, max_ctas);

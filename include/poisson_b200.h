@@ -144,6 +144,9 @@ typedef struct pb_solve_options {
   int ap_mode;        /* TMA persistent kernel, constant-coefficient tiles: 1 = phase AB stores Ap and phase C reloads
                          it; 2 = phase C recomputes Ap from the p box (same bits, 16 B/node less traffic);
                          0 = the library's default */
+  int no_balance;     /* TMA persistent kernel: 1 = tiles go to CTAs cyclically; 0 = cost-balanced assignment (the
+                         default; the sums are then taken in a different order, so results differ in the last bits from
+                         a cyclic run) */
 } pb_solve_options;
 
 int pb_cuda_device_count(void);

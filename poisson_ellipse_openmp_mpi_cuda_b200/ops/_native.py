@@ -79,6 +79,7 @@ class SolveOptions(C.Structure):
         ("l2_hints", C.c_int),
         ("full_coefficients", C.c_int),
         ("ap_mode", C.c_int),
+        ("no_balance", C.c_int),
     ]
 
 

@@ -208,9 +208,10 @@ def test_coefficient_classes_are_bit_identical_to_streamed_coefficients(pg, tile
     streaming the fp64 coefficient boxes."""
     for grid in [(96, 200), (400, 600)]:
         s = _solver(*grid, *pg)
-        ra = s.solve(tile_rows=tile_rows, full_coefficients=True)
+        # (cyclic tile -> CTA map for both: the balanced map depends on the classes, and with it the summation order)
+        ra = s.solve(tile_rows=tile_rows, full_coefficients=True, balance=False)
         wa = s.solution_host().clone()
-        rb = s.solve(tile_rows=tile_rows)
+        rb = s.solve(tile_rows=tile_rows, balance=False)
         wb = s.solution_host()
         assert ra["iters"] == rb["iters"]
         assert torch.equal(wa, wb)
