@@ -241,11 +241,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       put(at + 1, li0 + TX, m1 | ((recompute_ap && m1 != 2 && (code & 128)) ? kItemRecomp : 0));
       return 2;
     };
-    // relative cost of a super-tile, phases AB + C, in 0.1 us (measured: tall item 6.8 us, 32-row item with constant
-    // coefficients 3.8 us, mixed 4.5 us)
+    // relative cost of a super-tile, phases AB + C, in 0.1 us (least-squares fit of the per-CTA busy times at 4096^2,
+    // bench/experiments/cta_balance.py: tall item 6.3 us, 32-row item with constant coefficients 4.1 us, mixed 4.9 us)
     auto cost = [&](int code) -> int {
-      if (code & 32) return 68;
-      return ((code & 3) == 2 ? 45 : 38) + ((code & 16) ? (((code >> 2) & 3) == 2 ? 45 : 38) : 0);
+      if (code & 32) return 63;
+      return ((code & 3) == 2 ? 49 : 41) + ((code & 16) ? (((code >> 2) & 3) == 2 ? 49 : 41) : 0);
     };
     unsigned char* tcode = reinterpret_cast<unsigned char*>(ctl) + kTileCodeOffset;
     const bool balance = CC && balance_mode != 0 && ncta > 1 && ntiles <= kTileCodeBytes;

@@ -28,8 +28,9 @@ namespace pb {
 
 constexpr int kResMaxPerThread = 16;  // nodes per thread: sub-blocks of up to 8192 nodes
 
+// p with ring, r, w, D on the ring, and one class byte per cell of the sub-block and its ring
 __host__ __device__ inline size_t resident_smem_doubles(int sx, int sy) {
-  return (size_t)(sx + 2) * (sy + 2) + 2 * (size_t)sx * sy + 2 * (size_t)(sx + sy);
+  return (size_t)(sx + 2) * (sy + 2) + 2 * (size_t)sx * sy + 2 * (size_t)(sx + sy) + ((size_t)(sx + 2) * (sy + 2) + 7) / 8;
 }
 
 template <int DIV>
@@ -66,6 +67,10 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
   double* R = P + (size_t)(sx + 2) * PP;  // sx x sy
   double* W = R + (size_t)sx * sy;        // sx x sy
   double* Dr = W + (size_t)sx * sy;       // D on the ring: top cy | bottom cy | left cx | right cx (offsets sy, 2 sy, 2 sy + sx)
+  // class bytes of the sub-block and its ring (same (row + 1) * PP + col + 1 indexing as P): a mixed sub-block takes
+  // a, b, D of a cell from its class (1, 1/eps, the two diagonals) and reads the arrays only for the few cells whose
+  // class says "anything else" -- the cut faces -- instead of 6 values per node and iteration from L2
+  unsigned char* C8 = reinterpret_cast<unsigned char*>(Dr + 2 * (size_t)(sx + sy));
 
   const double delta = ctl->delta;
   const long long max_iter = ctl->max_iter;
@@ -95,8 +100,12 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
   const double cf = mode == 1 ? inv_eps : 1.0;
   const double dg = mode == 1 ? diag_out : diag_in, rc = __drcp_rn(dg);
 
-  // ---- load: r -> R, w = 0, p = 0 (ring included), D on the ring ----
-  for (int e = threadIdx.x; e < (sx + 2) * PP; e += kThreads) P[e] = 0.0;
+  // ---- load: r -> R, w = 0, p = 0 (ring included), D on the ring, class bytes ----
+  for (int e = threadIdx.x; e < (sx + 2) * PP; e += kThreads) {
+    P[e] = 0.0;
+    const int row = e / PP, col = e - row * PP;
+    C8[e] = (cx > 0 && row <= cx + 1 && col <= cy + 1) ? c.cls[(size_t)(li0 - 1 + row) * S + (lj0 - 1 + col + kColOff)] : 0;
+  }
   for (int e = threadIdx.x; e < sx * sy; e += kThreads) {
     const int row = e >> sy_log2, col = e & (sy - 1);
     R[e] = (row < cx && col < cy) ? c.r[(size_t)(li0 + row) * S + (lj0 + col + kColOff)] : 0.0;
@@ -138,10 +147,16 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     acc += now_ - t_prev;                             \
     t_prev = now_;                                    \
   }
-  // D of an owned node: the class constant, or the array for a mixed sub-block
-  auto node_D = [&](size_t g) -> double { return mode == 2 ? __ldg(&c.D[g]) : dg; };
-  auto div_D = [&](double r, size_t g) -> double {
-    return mode == 2 ? div_var<DIV>(r, __ldg(&c.D[g])) : div_known<DIV>(r, dg, rc);
+  // value of a coefficient from its 2-bit class: 0 -> v_in, 1 -> v_out, else the array
+  auto by_class = [&](unsigned int k, double v_in, double v_out, const double* arr, size_t g) -> double {
+    return k == 0u ? v_in : (k == 1u ? v_out : __ldg(arr + g));
+  };
+  // D of the owned node at P-cell `pe`: the sub-block's constant, or by the cell's class for a mixed sub-block
+  auto node_D = [&](int pe, size_t g) -> double {
+    return mode == 2 ? by_class((C8[pe] >> 4) & 3u, diag_in, diag_out, c.D, g) : dg;
+  };
+  auto div_D = [&](double r, int pe, size_t g) -> double {
+    return mode == 2 ? div_var<DIV>(r, by_class((C8[pe] >> 4) & 3u, diag_in, diag_out, c.D, g)) : div_known<DIV>(r, dg, rc);
   };
 
   // ---- init: zr_old = (D^-1 r, r) ----
@@ -153,7 +168,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
       const int row = e >> sy_log2, col = e & (sy - 1);
       if (row < cx && col < cy) {
         const double r = R[e];
-        v[0] = fma(safe_div(r, node_D((size_t)(li0 + row) * S + (lj0 + col + kColOff))), r, v[0]);
+        v[0] = fma(safe_div(r, node_D((row + 1) * PP + col + 1, (size_t)(li0 + row) * S + (lj0 + col + kColOff))), r, v[0]);
       }
     }
     ++seq;
@@ -211,7 +226,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
       const int row = e >> sy_log2, col = e & (sy - 1);
       if (row < cx && col < cy) {
         const int pe = (row + 1) * PP + col + 1;
-        P[pe] = fma(beta, P[pe], div_D(R[e], (size_t)(li0 + row) * S + (lj0 + col + kColOff)));
+        P[pe] = fma(beta, P[pe], div_D(R[e], pe, (size_t)(li0 + row) * S + (lj0 + col + kColOff)));
       }
     }
     __syncthreads();
@@ -228,7 +243,10 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
         double a_c = cf, a_ip = cf, b_c = cf, b_jp = cf;
         if (mode == 2) {
           const size_t g = (size_t)(li0 + row) * S + (lj0 + col + kColOff);
-          a_c = __ldg(&c.a[g]), a_ip = __ldg(&c.a[g + S]), b_c = __ldg(&c.b[g]), b_jp = __ldg(&c.b[g + 1]);
+          const int pe = (row + 1) * PP + col + 1;
+          const unsigned int k0 = C8[pe], kx = C8[pe + PP], ky = C8[pe + 1];
+          a_c = by_class(k0 & 3u, 1.0, inv_eps, c.a, g), a_ip = by_class(kx & 3u, 1.0, inv_eps, c.a, g + S);
+          b_c = by_class((k0 >> 2) & 3u, 1.0, inv_eps, c.b, g), b_jp = by_class((ky >> 2) & 3u, 1.0, inv_eps, c.b, g + 1);
         }
         ap[q] = stencil_value<DIV>(K, s[0], s[-PP], s[PP], s[-1], s[1], a_c, a_ip, b_c, b_jp);
         acc_ab = fma(ap[q], s[0], acc_ab);
@@ -269,7 +287,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
         R[e] = r_new;
         const double dw = __dsub_rn(w_new, w_old);
         acc_d = fma(dw, dw, acc_d);
-        acc_zr = fma(div_D(r_new, g), r_new, acc_zr);
+        acc_zr = fma(div_D(r_new, (row + 1) * PP + col + 1, g), r_new, acc_zr);
         // rim of the sub-block: the neighbouring CTAs read it from the global array in their next phase AB
         if (row == 0 || row == cx - 1 || col == 0 || col == cy - 1) {
           c.r[g] = r_new;
