@@ -33,12 +33,17 @@ bool Solver::resident_cut(ResidentCut* cut) const {
 void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   if (!fabric_complete_) throw std::runtime_error("persistent solve needs every rank's arena (open_peer) first");
   const int exact = opt.exact_div;
-  // Blocks that fit into the SMs' shared memory run in the resident kernel: no field data moves through L2 / HBM
-  // during the iteration.  Options that only exist for the TMA kernel (tile height, Ap mode, streamed coefficients,
-  // L2 hints) pin that kernel, as does method = persistent_tma.
+  // Small blocks run in the resident kernel: no field data moves through L2 / HBM during the iteration.  It is
+  // taken automatically up to 128 Ki nodes per rank, where it measured faster than the TMA kernel (100 x 1200: 11.7
+  // against 12.1 us per iteration, 160 x 160: 10.5 against 11.9); above that the sub-blocks the ellipse's boundary
+  // crosses (a third of the CTAs at 800 x 1200) take twice as long as the others and the TMA kernel wins (22.2
+  // against 30.9 us), so there it runs only on request (method = resident).  Options that only exist for the TMA
+  // kernel (tile height, Ap mode, streamed coefficients, L2 hints) pin that kernel, as does method = persistent_tma.
   ResidentCut cut{};
+  const LocalBlock b0 = make_local_block(grid_.M, grid_.N, pg_, 0);
+  const bool small = (long long)b0.nx * b0.ny <= 128 * 1024;
   const bool want_resident = opt.method == kMethodResident ||
-                             (opt.method == kMethodPersistent && opt.tile_rows == 0 && opt.ap_mode == 0 &&
+                             (opt.method == kMethodPersistent && small && opt.tile_rows == 0 && opt.ap_mode == 0 &&
                               opt.compressed != 0 && opt.l2_hints == 0 && std::getenv("PB_NO_RESIDENT") == nullptr);
   if (want_resident && resident_cut(&cut)) {
     for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));

@@ -117,8 +117,8 @@ int pb_cpu_error_local(int M, int N, const pb_block* blk, const double* w, doubl
 typedef struct pb_solver pb_solver;
 
 #define PB_METHOD_PERSISTENT 0   /* one cooperative launch per solve, fused halo + reductions: the resident kernel for blocks
-                                    that fit on chip (unless tile_rows / ap_mode / l2_hints / full_coefficients are set),
-                                    else the TMA kernel */
+                                    of up to 128 Ki nodes per rank (unless tile_rows / ap_mode / l2_hints /
+                                    full_coefficients are set), else the TMA kernel */
 #define PB_METHOD_STEP_FUSED 1   /* separate launches, fused p-update + stencil (single rank) */
 #define PB_METHOD_STEP_CLASSIC 2 /* separate launches, reference-like 3-kernel structure (single rank) */
 #define PB_METHOD_PERSISTENT_LDG 3 /* persistent kernel with plain global loads instead of TMA pipelines */

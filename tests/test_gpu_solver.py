@@ -149,7 +149,7 @@ def test_repeated_solves_and_max_iter():
     s.close()
 
 
-@pytest.mark.parametrize("method,kernel", [("persistent", "resident"), ("persistent_tma", "tma")])
+@pytest.mark.parametrize("method,kernel", [("persistent", "tma"), ("resident", "resident")])
 def test_large_grid_800x1200(method, kernel):
     s = _solver(800, 1200)
     res = s.solve(method=method)
@@ -159,6 +159,9 @@ def test_large_grid_800x1200(method, kernel):
 
 
 def test_resident_kernel_is_refused_for_blocks_that_do_not_fit():
+    s = _solver(160, 160)
+    assert s.solve()["kernel"] == "resident"  # auto: small blocks stay on chip
+    s.close()
     s = _solver(2048, 2048)
     assert s.solve(max_iter=5)["kernel"] == "tma"  # auto: too large for shared memory
     with pytest.raises(RuntimeError, match="does not fit"):
