@@ -322,6 +322,96 @@ __device__ __forceinline__ double warp_sum_all(double x) {
   return x;
 }
 
+// ---- clusters of two CTAs: the first level of the star --------------------------------------------------------------
+// When the kernel is launched with thread-block clusters of two (148 = 2 x 74 CTAs pack perfectly), the odd CTA of a
+// pair does not send a record through L2: lane 0 releases the CTA's stores with its fence and writes the CTA's sums
+// straight into the even CTA's shared memory (distributed shared memory, st.async completing on the even CTA's
+// mbarrier); the even CTA adds them to its own and sends ONE record for the pair.  Half as many records travel to
+// CTA 0, and the odd CTA's fence runs beside the even one's instead of in front of a store CTA 0 waits for.
+// Measured with bench/experiments/hop_latency.cu (148 CTAs, fenced): 1.8 us per round against 2.4-2.7 us.
+struct PairState {
+  unsigned long long bar;     // mbarrier of the even CTA: one arrival (its own) + the bytes of the partner's sums
+  double vals[kRedValues];    // the odd CTA's sums
+  unsigned int round;         // reductions so far in this launch (phase parity of `bar`)
+};
+__device__ __forceinline__ PairState* star_pair_state() {
+  __shared__ __align__(16) PairState st;
+  return &st;
+}
+__device__ __forceinline__ unsigned int pb_smem_u32(const void* p) { return (unsigned int)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned int mapa_shared_cluster(unsigned int addr, unsigned int cta_rank) {
+  unsigned int r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ void st_async_cluster_b64(unsigned int remote_addr, unsigned long long v, unsigned int remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr), "l"(v),
+               "r"(remote_bar)
+               : "memory");
+}
+// all threads of both CTAs of the cluster (kernel start and end only)
+__device__ __forceinline__ void cluster_barrier_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Kernel start (all threads; `pair` is the kernel's launch mode): the even CTA's mbarrier must exist before its
+// partner's first write.  Kernel end (all threads, on EVERY exit path): nobody leaves while its partner may still
+// write into its shared memory.
+__device__ __forceinline__ void star_pair_init(int pair) {
+  if (!pair) return;
+  PairState* ps = star_pair_state();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(pb_smem_u32(&ps->bar)) : "memory");
+    ps->round = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  cluster_barrier_all();
+}
+__device__ __forceinline__ void star_pair_exit(int pair) {
+  if (pair) cluster_barrier_all();
+}
+// lane 0 of warp 0 of an even CTA: wait for the partner's sums of this round (bounded) and add them
+template <int NV>
+__device__ __forceinline__ bool star_pair_receive(double (&tot)[NV], unsigned long long limit) {
+  PairState* ps = star_pair_state();
+  const unsigned int bar = pb_smem_u32(&ps->bar), parity = ps->round & 1u;
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned int)(NV * 8)) : "memory");
+  unsigned long long t0 = 0;
+  unsigned int spins = 0;
+  bool ok = true;
+  while (true) {
+    unsigned int done;
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if ((++spins & 0xffu) == 0u) {
+      const unsigned long long now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > limit) {
+        ok = false;
+        break;
+      }
+    }
+  }
+  ps->round += 1;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) tot[k] += ps->vals[k];  // fixed order: even CTA + odd CTA
+  return ok;
+}
+// lane 0 of warp 0 of an odd CTA: release, then hand the sums to the even CTA (cluster rank 0)
+template <int NV>
+__device__ __forceinline__ void star_pair_send(const double (&tot)[NV]) {
+  PairState* ps = star_pair_state();
+  fence_acq_rel_gpu();  // release: this CTA's stores of the phase (cumulative over the caller's barrier)
+  const unsigned int rvals = mapa_shared_cluster(pb_smem_u32(&ps->vals[0]), 0), rbar = mapa_shared_cluster(pb_smem_u32(&ps->bar), 0);
+#pragma unroll
+  for (int k = 0; k < NV; ++k) st_async_cluster_b64(rvals + 8u * k, (unsigned long long)__double_as_longlong(tot[k]), rbar);
+}
+
 #ifdef PB_VAR_NOINLINE  // experiment only
 #define PB_EXCHANGE_INLINE __noinline__
 #else
@@ -348,7 +438,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // TRACE (micro-benchmark only): thread 0 adds the clock64 distance between the numbered steps to trace[3..7].
 template <int NV, bool TRACE>
 __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_io, unsigned long long* gbuf, unsigned int seq,
-                                                 int cta, int ncta, unsigned long long limit, long long* trace) {
+                                                 int cta, int ncta, int pair, unsigned long long limit, long long* trace) {
   const RankCtx& c = *cp;
   const int lane = threadIdx.x & 31;
   long long tr_prev = 0;
@@ -369,15 +459,23 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
   double tot[NV];
 #pragma unroll
   for (int k = 0; k < NV; ++k) tot[k] = tot_io[k];
+  // clusters of two: the even CTA of a pair speaks for both (record index = pair index), the odd one has handed its
+  // sums over already and only waits for the result
+  const int rec = pair ? cta >> 1 : cta, nrec = pair ? ncta >> 1 : ncta;
+  if (pair && !(cta & 1) && lane == 0) ok = star_pair_receive<NV>(tot, limit);
   if (cta != 0) {
     // ---- level 1: release + record; level 3: wait for the result ----
     if (lane == 0) {
-      fence_acq_rel_gpu();  // release: this CTA's stores of the phase (cumulative over the caller's barrier)
+      if (pair && (cta & 1)) {
+        star_pair_send<NV>(tot);
+      } else {
+        fence_acq_rel_gpu();  // release: this CTA's (and its partner's) stores of the phase
 #pragma unroll
-      for (int k = 0; k < NV; ++k) {
-        unsigned long long w0, w1;
-        ll_encode(tot[k], seq, w0, w1);
-        st_relaxed_gpu_v2_u64(ll1 + k * kValStride + (size_t)cta * 2, w0, w1);
+        for (int k = 0; k < NV; ++k) {
+          unsigned long long w0, w1;
+          ll_encode(tot[k], ok ? seq : seq ^ 0x80000000u, w0, w1);
+          st_relaxed_gpu_v2_u64(ll1 + k * kValStride + (size_t)rec * 2, w0, w1);
+        }
       }
       PB_TRACE(3);  // release fence + record store
       if (c.nranks == 1) {
@@ -419,7 +517,7 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
       double acc[NV];
       unsigned long long t0 = 0;
       unsigned int spins = 0;
-      const int nfast = min(ncta, kGatherSlots);
+      const int nfast = min(nrec, kGatherSlots);
       while (true) {
         bool all = true;
         for (int i = lane == 0 ? 32 : lane; i < nfast; i += 32) {
@@ -437,7 +535,7 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
             acc[k] += ll_decode(w.x, w.y);
           }
         }
-        for (int i = lane + kGatherSlots; i < ncta; i += 32) {
+        for (int i = lane + kGatherSlots; i < nrec; i += 32) {
           double v[NV];
           all = ll_peek<NV, false>(ll1 + (size_t)i * 2, kValStride, seq, v) && all;
 #pragma unroll
@@ -455,6 +553,7 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
       }
 #pragma unroll
       for (int k = 0; k < NV; ++k) tot[k] = warp_sum_all(acc[k]);
+      ok = __all_sync(0xffffffffu, ok);  // lane 0 may have timed out waiting for its partner CTA
     }
     PB_TRACE(4);  // gather of the CTA records
     if (c.nranks > 1) {
@@ -502,9 +601,10 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
   return ok;
 }
 
+// `pair`: the kernel runs with clusters of two CTAs (star_pair_init was called); ncta is then even.
 template <int NV, bool TRACE = false>
 __device__ __forceinline__ RedResult star_sum(const RankCtx& c, double (&val)[NV], unsigned int seq, int cta, int ncta,
-                                              unsigned long long limit, double* smem, long long* trace = nullptr) {
+                                              unsigned long long limit, double* smem, long long* trace = nullptr, int pair = 0) {
   static_assert(NV <= kRedValues, "too many values");
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;  // nwarps <= 16
   long long tr_prev = 0;
@@ -560,7 +660,7 @@ __device__ __forceinline__ RedResult star_sum(const RankCtx& c, double (&val)[NV
       for (int k = 0; k < NV; ++k) io[k] = tot[k];
     }
     __syncwarp();
-    const bool ok = star_exchange<NV, TRACE>(&c, io, star_gather_buf(), seq, cta, ncta, limit, trace);
+    const bool ok = star_exchange<NV, TRACE>(&c, io, star_gather_buf(), seq, cta, ncta, pair, limit, trace);
     if (lane == 0) {
 #pragma unroll
       for (int k = 0; k < NV; ++k) smem[64 + k] = io[k];

@@ -14,6 +14,10 @@ cudaError_t launch_error_report(const RankCtx* d_ctx, const RankCtx& h_ctx, cuda
 cudaError_t launch_gather_interior(const double* w, int nx, int ny, int pitch, double* out, long long ld,
                                    cudaStream_t stream);
 
+// cooperative launch, as clusters of two CTAs where possible (persistent.cu); *pair_arg (one of the kernel's
+// arguments) tells the kernel which it got
+cudaError_t launch_cooperative_pairs(const void* fn, int nvirt, int ctas_per_rank, int threads, void** args, int* pair_arg,
+                                     size_t smem, cudaStream_t stream);
 // communication micro-benchmark (persistent.cu): reductions alone (mode 0) or halo stores + reduction (mode 1)
 cudaError_t launch_xgpu_bench(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int iters, int mode, int edge,
                               cudaStream_t stream);

@@ -16,6 +16,8 @@
 // cooperative launch guarantees that all CTAs that wait for each other are co-resident.
 #include <cooperative_groups.h>
 
+#include <cstdlib>
+
 #include "launch.h"
 #include "phases.cuh"
 
@@ -171,7 +173,7 @@ pcg_persistent_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank) {
 //           per step in the per-CTA report area (pb_solver_cta_report)
 // CTA 0 of each rank measures the whole loop with %globaltimer -> Control::t_total (ns).
 __global__ void __launch_bounds__(kThreads, 1)
-xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters, int mode, int edge) {
+xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters, int mode, int edge, int pair_mode) {
   __shared__ RankCtx c;
   __shared__ double s_red[80];
   const int vrank = blockIdx.x / ctas_per_rank;
@@ -182,6 +184,7 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     for (int i = threadIdx.x; i < (int)(sizeof(RankCtx) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
   }
   __syncthreads();
+  star_pair_init(pair_mode);
   unsigned int seq = c.ctl->red_seq, arrive_target = 0;
   const unsigned int hseq = c.ctl->halo_seq;
   const unsigned long long wd_limit = c.ctl->watchdog_ns ? c.ctl->watchdog_ns : kDefaultWatchdogNs;
@@ -256,8 +259,8 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     double v[2] = {threadIdx.x == 0 ? 1.0 : 0.0, 0.0};
     ++seq;
     arrive_target += ncta;
-    const RedResult rr = mode == 5 ? star_sum<2, true>(c, v, seq, cta, ncta, wd_limit, s_red, tr)
-                         : mode >= 3 ? star_sum<2>(c, v, seq, cta, ncta, wd_limit, s_red)
+    const RedResult rr = mode == 5 ? star_sum<2, true>(c, v, seq, cta, ncta, wd_limit, s_red, tr, pair_mode)
+                         : mode >= 3 ? star_sum<2>(c, v, seq, cta, ncta, wd_limit, s_red, nullptr, pair_mode)
                                    : cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr,
                                                        mode == 1 && c.sys_scope != 0);
     ok = rr.ok;
@@ -277,6 +280,7 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(c.ctl) + kCtaTimesOffset) + kCtaTimeWords * cta;
     for (int i = 0; i < 8; ++i) mine[i] = (double)tr[i] / (double)max(1, iters);
   }
+  star_pair_exit(pair_mode);
   if (cta == 0 && threadIdx.x == 0) {
     c.ctl->t_total = globaltimer_ns() - t0;
     c.ctl->red_seq = seq;
@@ -288,9 +292,40 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
 
 cudaError_t launch_xgpu_bench(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int iters, int mode, int edge,
                               cudaStream_t stream) {
-  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&iters, (void*)&mode, (void*)&edge};
-  return cudaLaunchCooperativeKernel((const void*)xgpu_bench_kernel, dim3(nvirt * ctas_per_rank), dim3(kThreads), args,
-                                     0, stream);
+  int pair = 0;
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&iters, (void*)&mode, (void*)&edge, (void*)&pair};
+  if (mode < 3)  // the counter + aggregator reduction knows nothing about clusters
+    return cudaLaunchCooperativeKernel((const void*)xgpu_bench_kernel, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, 0, stream);
+  return launch_cooperative_pairs((const void*)xgpu_bench_kernel, nvirt, ctas_per_rank, kThreads, args, &pair, 0, stream);
+}
+
+// Cooperative launch of nvirt * ctas_per_rank CTAs, as thread-block clusters of two when every rank has an even
+// number of CTAs (*pair_arg, which must be one of the kernel's arguments, is set to 1 then) and PB_NO_CLUSTERS is not
+// set; plain cooperative launch otherwise or when the clustered launch is refused.
+cudaError_t launch_cooperative_pairs(const void* fn, int nvirt, int ctas_per_rank, int threads, void** args, int* pair_arg,
+                                     size_t smem, cudaStream_t stream) {
+  static const bool disabled = std::getenv("PB_NO_CLUSTERS") != nullptr;
+  *pair_arg = 0;
+  if (!disabled && ctas_per_rank >= 2 && (ctas_per_rank & 1) == 0) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(nvirt * ctas_per_rank);
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2, attr[1].val.clusterDim.y = 1, attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    *pair_arg = 1;
+    const cudaError_t e = cudaLaunchKernelExC(&cfg, fn, args);
+    if (e == cudaSuccess) return e;
+    cudaGetLastError();  // refused (e.g. not all clusters co-resident): fall back to single CTAs
+    *pair_arg = 0;
+  }
+  return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(threads), args, smem, stream);
 }
 
 size_t persistent_smem_bytes() { return sizeof(double) * kSmemTile; }

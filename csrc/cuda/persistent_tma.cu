@@ -90,7 +90,7 @@ struct TmaCfg {
 template <int TX, int DIV, bool CC>
 __global__ void __launch_bounds__(kThreads, 1)
 pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int map_variant, int l2_hints,
-                          int recompute_ap, int tall_mode, int balance_mode) {
+                          int recompute_ap, int tall_mode, int balance_mode, int pair_mode) {
   using Cfg = TmaCfg<TX>;
   constexpr int TY = Cfg::TY, EC = Cfg::EC, BC = Cfg::BC, S = Cfg::kStages;
   __shared__ RankCtx c;
@@ -123,6 +123,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     mbar_fence_init();
   }
   __syncthreads();
+  star_pair_init(pair_mode);  // clusters of two CTAs: the partner's mbarrier exists from here on
   // s_dyn is declared __align__(128); deriving every stage pointer from it by plain pointer arithmetic keeps
   // the accesses in the shared address space (LDS/STS instead of generic LD/ST)
   unsigned char* const stage_base = s_dyn;
@@ -148,7 +149,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 #define PB_RED(nv) cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false)
 #else
 #define PB_RED_PRE
-#define PB_RED(nv) star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red)
+#define PB_RED(nv) star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode)
 #endif
   const double delta = ctl->delta;
   const long long max_iter = ctl->max_iter;
@@ -490,6 +491,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         ctl->status = PB_STATUS_WATCHDOG;
         ctl->red_seq = seq;
       }
+      star_pair_exit(pair_mode);
       return;
     }
     zr_old = rr.v[0] * h1h2;
@@ -881,6 +883,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     ctl->t_total = globaltimer_ns() - t_start;
     ctl->t_halo = s_t_halo;
   }
+  star_pair_exit(pair_mode);
 #undef PB_STAMP
 #undef PB_RED
 #undef PB_RED_PRE
@@ -894,9 +897,10 @@ static cudaError_t launch_variant(const RankCtx* d_ctxs, int nvirt, int ctas_per
   const size_t smem = TmaCfg<TX>::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
+  int pair = 0;
   void* args[] = {(void*)&d_ctxs, (void*)&ctas_per_rank, (void*)&variant, (void*)&l2_hints, (void*)&recompute_ap, (void*)&tall,
-                  (void*)&balance};
-  return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(kThreads), args, smem, stream);
+                  (void*)&balance, (void*)&pair};
+  return launch_cooperative_pairs(fn, nvirt, ctas_per_rank, kThreads, args, &pair, smem, stream);
 }
 
 template <int TX, bool CC>

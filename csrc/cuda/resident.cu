@@ -35,7 +35,7 @@ __host__ __device__ inline size_t resident_smem_doubles(int sx, int sy) {
 
 template <int DIV>
 __global__ void __launch_bounds__(kThreads, 1)
-pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx, int sy_log2, int bx, int by) {
+pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx, int sy_log2, int bx, int by, int pair_mode) {
   __shared__ RankCtx c;
   __shared__ double s_red[80];
   __shared__ unsigned long long s_wd_limit;
@@ -54,6 +54,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     s_wd_limit = wd ? wd : kDefaultWatchdogNs;
   }
   __syncthreads();
+  star_pair_init(pair_mode);
   Control* ctl = c.ctl;
   const int S = c.pitch;
   const int sy = 1 << sy_log2, PP = sy + 2;
@@ -172,12 +173,13 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
       }
     }
     ++seq;
-    const RedResult rr = star_sum<1>(c, v, seq, cta, ncta, s_wd_limit, s_red);
+    const RedResult rr = star_sum<1>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode);
     if (!rr.ok) {
       if (threadIdx.x == 0 && cta == 0) {
         ctl->status = PB_STATUS_WATCHDOG;
         ctl->red_seq = seq;
       }
+      star_pair_exit(pair_mode);
       return;
     }
     zr_old = rr.v[0] * h1h2;
@@ -256,7 +258,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     {
       double v[1] = {acc_ab};
       ++seq;
-      const RedResult rr = star_sum<1>(c, v, seq, cta, ncta, s_wd_limit, s_red);
+      const RedResult rr = star_sum<1>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode);
       PB_STAMP(t_r1);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -313,7 +315,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     {
       double v[2] = {acc_d, acc_zr};
       ++seq;
-      const RedResult rr = star_sum<2>(c, v, seq, cta, ncta, s_wd_limit, s_red);
+      const RedResult rr = star_sum<2>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode);
       PB_STAMP(t_r2);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -369,6 +371,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     ctl->t_total = globaltimer_ns() - t_start;
     ctl->t_halo = t_halo;
   }
+  star_pair_exit(pair_mode);
 #undef PB_STAMP
 }
 
@@ -410,9 +413,9 @@ cudaError_t launch_resident(const RankCtx* d_ctxs, int nvirt, const ResidentCut&
   const size_t smem = resident_smem_bytes(cut);
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  int ctas = cut.bx * cut.by, sx = cut.sx, lg = cut.sy_log2, bx = cut.bx, by = cut.by;
-  void* args[] = {(void*)&d_ctxs, (void*)&ctas, (void*)&sx, (void*)&lg, (void*)&bx, (void*)&by};
-  return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas), dim3(kThreads), args, smem, stream);
+  int ctas = cut.bx * cut.by, sx = cut.sx, lg = cut.sy_log2, bx = cut.bx, by = cut.by, pair = 0;
+  void* args[] = {(void*)&d_ctxs, (void*)&ctas, (void*)&sx, (void*)&lg, (void*)&bx, (void*)&by, (void*)&pair};
+  return launch_cooperative_pairs(fn, nvirt, ctas, kThreads, args, &pair, smem, stream);
 }
 
 }  // namespace pb

@@ -67,6 +67,7 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
   int ctas = (per_sm * sm_count_) / nlocal();
   ctas = std::min(ctas, kMaxCtas);
   ctas = std::min(ctas, max_tiles);
+  if (tma && ctas > 2) ctas &= ~1;  // an even number of CTAs per rank: the kernel then runs as clusters of two
   if (ctas < 1) throw std::runtime_error("too many virtual ranks for one cooperative launch");
   last_ctas_per_rank_ = ctas;
   for (int l = 0; l < nlocal(); ++l) {
@@ -231,6 +232,7 @@ void Solver::xgpu_bench(int iters, int mode, int edge, int ctas, cudaStream_t st
   PB_CUDA_CHECK(cudaSetDevice(device_));
   if (ctas <= 0) ctas = sm_count_ / nlocal();
   ctas = std::min(ctas, kMaxCtas);
+  if (ctas > 2) ctas &= ~1;
   last_ctas_per_rank_ = ctas;
   for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
   PB_CUDA_CHECK(launch_xgpu_bench(dctx_, nlocal(), ctas, iters, mode, edge, stream));
