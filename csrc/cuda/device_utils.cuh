@@ -328,7 +328,9 @@ __device__ __forceinline__ double warp_sum_all(double x) {
 // straight into the even CTA's shared memory (distributed shared memory, st.async completing on the even CTA's
 // mbarrier); the even CTA adds them to its own and sends ONE record for the pair.  Half as many records travel to
 // CTA 0, and the odd CTA's fence runs beside the even one's instead of in front of a store CTA 0 waits for.
-// Measured with bench/experiments/hop_latency.cu (148 CTAs, fenced): 1.8 us per round against 2.4-2.7 us.
+// Measured: the stand-alone model (bench/experiments/hop_latency.cu, 148 one-warp CTAs, fenced) gains 0.6-0.8 us per
+// round, but inside the real kernels the reduction gets slower (3.52 against 3.31 us), so the launchers use clusters
+// only on request (PB_CLUSTERS=1, see launch_cooperative_pairs).
 struct PairState {
   unsigned long long bar;     // mbarrier of the even CTA: one arrival (its own) + the bytes of the partner's sums
   double vals[kRedValues];    // the odd CTA's sums

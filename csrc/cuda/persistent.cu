@@ -299,14 +299,17 @@ cudaError_t launch_xgpu_bench(const RankCtx* d_ctxs, int nvirt, int ctas_per_ran
   return launch_cooperative_pairs((const void*)xgpu_bench_kernel, nvirt, ctas_per_rank, kThreads, args, &pair, 0, stream);
 }
 
-// Cooperative launch of nvirt * ctas_per_rank CTAs, as thread-block clusters of two when every rank has an even
-// number of CTAs (*pair_arg, which must be one of the kernel's arguments, is set to 1 then) and PB_NO_CLUSTERS is not
-// set; plain cooperative launch otherwise or when the clustered launch is refused.
+// Cooperative launch of nvirt * ctas_per_rank CTAs; with PB_CLUSTERS=1 in the environment as thread-block clusters of
+// two when every rank has an even number of CTAs (*pair_arg, which must be one of the kernel's arguments, is set to 1
+// then), falling back to the plain launch when the clustered one is refused.  Off by default: measured on a B200
+// the pair level makes the reduction slower inside the real kernels (3.52 against 3.31 us per reduction with 148 CTAs
+// of 512 threads; 800 x 1200: 23.5 against 22.3 us per iteration; 4096 x 512: 36.9 against 35.7), although the
+// stand-alone model of it (bench/experiments/hop_latency.cu, one warp per CTA) gains 0.6-0.8 us per round.
 cudaError_t launch_cooperative_pairs(const void* fn, int nvirt, int ctas_per_rank, int threads, void** args, int* pair_arg,
                                      size_t smem, cudaStream_t stream) {
-  static const bool disabled = std::getenv("PB_NO_CLUSTERS") != nullptr;
+  static const bool enabled = std::getenv("PB_CLUSTERS") != nullptr;
   *pair_arg = 0;
-  if (!disabled && ctas_per_rank >= 2 && (ctas_per_rank & 1) == 0) {
+  if (enabled && ctas_per_rank >= 2 && (ctas_per_rank & 1) == 0) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(nvirt * ctas_per_rank);
     cfg.blockDim = dim3(threads);
