@@ -81,8 +81,12 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
   const double inv_eps = 1.0 / c.g.eps;
   const double diag_in = diag_from_faces(c.g, 1.0, 1.0, 1.0, 1.0);
   const double diag_out = diag_from_faces(c.g, inv_eps, inv_eps, inv_eps, inv_eps);
-  unsigned int seq = ctl->red_seq;
+  unsigned int seq = ctl->red_seq, arrive_target = 0;
   const unsigned int hseq = ctl->halo_seq;
+  const bool multi_rank = c.nranks > 1;  // several ranks: cross_rank_sum measured faster than the star (persistent_tma.cu)
+#define PB_RES_RED(nv)                                                                                          \
+  (arrive_target += ncta, multi_rank ? cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false) \
+                                     : star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode))
 
   // ---- coefficient class of the sub-block and its ring (corners excluded): 0 inside, 1 outside, 2 mixed ----
   int mode;
@@ -173,7 +177,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
       }
     }
     ++seq;
-    const RedResult rr = star_sum<1>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode);
+    const RedResult rr = PB_RES_RED(1);
     if (!rr.ok) {
       if (threadIdx.x == 0 && cta == 0) {
         ctl->status = PB_STATUS_WATCHDOG;
@@ -258,7 +262,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     {
       double v[1] = {acc_ab};
       ++seq;
-      const RedResult rr = star_sum<1>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode);
+      const RedResult rr = PB_RES_RED(1);
       PB_STAMP(t_r1);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -315,7 +319,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     {
       double v[2] = {acc_d, acc_zr};
       ++seq;
-      const RedResult rr = star_sum<2>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode);
+      const RedResult rr = PB_RES_RED(2);
       PB_STAMP(t_r2);
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -372,6 +376,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     ctl->t_halo = t_halo;
   }
   star_pair_exit(pair_mode);
+#undef PB_RES_RED
 #undef PB_STAMP
 }
 

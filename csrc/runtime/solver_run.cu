@@ -46,7 +46,10 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
                              (opt.method == kMethodPersistent && small && opt.tile_rows == 0 && opt.ap_mode == 0 &&
                               opt.compressed != 0 && opt.l2_hints == 0 && std::getenv("PB_NO_RESIDENT") == nullptr);
   if (want_resident && resident_cut(&cut)) {
-    for (int l = 0; l < nlocal(); ++l) PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));
+    for (int l = 0; l < nlocal(); ++l) {
+      PB_CUDA_CHECK(cudaMemsetAsync(hctx_[l].arrive, 0, 128, stream));
+      PB_CUDA_CHECK(cudaMemsetAsync(control(l)->red, 0, sizeof(double) * 4, stream));
+    }
     last_ctas_per_rank_ = cut.bx * cut.by;
     last_tile_rows_ = 0;
     last_kernel_ = "resident";
