@@ -8,18 +8,21 @@ cd "$(dirname "$0")/../.."
 OUT=gpurun_out/campaign_$N; mkdir -p $OUT
 if [ "$N" = 1 ]; then TR="python"; else TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541"; fi
 nvidia-smi --query-gpu=index,name,clocks.max.sm,power.limit --format=csv,noheader > $OUT/gpus.txt
-if [ "$N" != 1 ]; then timeout 600 python -m pytest tests/test_multi_gpu.py -m gpu -x -q > $OUT/pytest_multi_gpu.log 2>&1; tail -2 $OUT/pytest_multi_gpu.log; fi
+# QUICK=1: our arm and the CLI only (a re-measurement after a kernel change)
+if [ "$N" != 1 ] && [ -z "$QUICK" ]; then timeout 600 python -m pytest tests/test_multi_gpu.py -m gpu -x -q > $OUT/pytest_multi_gpu.log 2>&1; tail -2 $OUT/pytest_multi_gpu.log; fi
 timeout 300 $TR bench.py --gpus $N --steps $STEPS --warmup 3 > $OUT/bench_ours_4096.json 2> $OUT/bench_ours_4096.err
 timeout 300 $TR bench.py --gpus $N --steps $STEPS --warmup 3 --M 800 --N 1200 > $OUT/bench_ours_800x1200.json 2> $OUT/bench_ours_800.err
+if [ -z "$QUICK" ]; then
 timeout 600 $TR bench.py --impl reference --gpus $N --steps 2 --warmup 1 > $OUT/bench_reference_4096.json 2> $OUT/bench_ref_4096.err
 timeout 300 $TR bench.py --impl reference --gpus $N --steps 2 --warmup 1 --M 800 --N 1200 > $OUT/bench_reference_800x1200.json 2> $OUT/bench_ref_800.err
+fi
 B=poisson_ellipse_openmp_mpi_cuda_b200/bin/poisson_b200
 for g in "4096 4096" "800 1200"; do set -- $g; ( time $B $1 $2 --gpus $N ) > $OUT/cli_${1}x${2}.txt 2>&1; done
-if [ "$N" != 1 ]; then
+if [ "$N" != 1 ] && [ -z "$QUICK" ]; then
   SWEEP_ITERS=500 timeout 300 $TR bench/halo_allreduce_sweep.py > $OUT/halo_allreduce_sweep.jsonl 2> $OUT/sweep.err
   timeout 300 python bench/ref_comm_sweep.py --ranks $N --iters 100 > $OUT/ref_comm_sweep.jsonl 2> $OUT/ref_comm.err
 fi
-if [ "$N" = 8 ]; then timeout 400 $TR bench/scaling.py --configs weak --reps 1 > $OUT/weak_scaling.jsonl 2> $OUT/weak.err; fi
+if [ "$N" = 8 ] && [ -z "$QUICK" ]; then timeout 400 $TR bench/scaling.py --configs weak --reps 1 > $OUT/weak_scaling.jsonl 2> $OUT/weak.err; fi
 for f in $OUT/bench_*.json; do python - $f <<'PY'
 import json, sys
 try:
