@@ -99,9 +99,10 @@ def measured_hbm_gbs() -> tuple[float, str]:
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-# In-kernel all-reduce of two doubles, one reduction, microseconds by GPU count (bench/halo_allreduce_sweep.py, record
-# star; profiles/halo_allreduce_sweep_*gpu.jsonl).  The floor of an iteration is two of them.
-REDUCTION_FLOOR_US = {1: 3.3, 2: 5.0, 4: 5.5, 8: 6.0}
+# In-kernel all-reduce of two doubles, one reduction, microseconds by GPU count, as measured with
+# bench/halo_allreduce_sweep.py on this pool (profiles/r2/campaign_*gpu/halo_allreduce_sweep.jsonl; 1 GPU: record star,
+# several GPUs: counter + elected aggregator).  The latency floor of an iteration is two of them.
+REDUCTION_FLOOR_US = {1: 3.3, 2: 5.5, 4: 6.0, 8: 6.4}
 NVLINK_GBS_PER_DIRECTION = 900.0
 
 
