@@ -490,18 +490,21 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
       }
     }
     if (c.nranks > 1) {
-      // Several ranks: no result record.  Every CTA reads the ranks' records in its own slot area directly (lane rk
-      // polls rank rk's record) and adds them in rank order: one hop less than going through CTA 0 again (measured
-      // at 2 GPUs: 6.4 us with the extra hop against 5.3 us for cross_rank_sum, which also polls the slots directly).
+      // Several ranks: every CTA reads the ranks' records in its own slot area directly (lane rk polls rank rk's
+      // record) and adds them in rank order: one hop less than going through CTA 0 again.  But not before CTA 0 says
+      // that its gather is over (the result record, polled by one lane): nranks lanes per CTA spinning on the slot
+      // lines while CTA 0 still gathers slowed that gather down (8 GPUs: 9.6 us per reduction).
       const size_t slot_off = ((size_t)(seq & 1u) * kMaxRanks) * kSlotWords;
       double r[NV];
 #pragma unroll
       for (int k = 0; k < NV; ++k) r[k] = 0.0;
-      if (lane < c.nranks) {
-        ok = ll_poll<NV, true>(c.slots + slot_off + (size_t)lane * kSlotWords, 2, seq, limit, r);
-        // acquire through this rank's own record: CTA 0 stored it after its fence
-        if (lane == c.rank) (void)ld_acquire_gpu_u64(c.slots + slot_off + (size_t)lane * kSlotWords);
+      if (lane == 0) {
+        double dummy[1];
+        ok = ll_poll<1, false>(res, 2, seq, limit, dummy) && ok;
+        (void)ld_acquire_gpu_u64(res);  // acquire: CTA 0 stored it after its fence
       }
+      __syncwarp();
+      if (lane < c.nranks) ok = ll_poll<NV, true>(c.slots + slot_off + (size_t)lane * kSlotWords, 2, seq, limit, r) && ok;
       ok = __all_sync(0xffffffffu, ok);
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
@@ -573,6 +576,11 @@ __device__ PB_EXCHANGE_INLINE bool star_exchange(const RankCtx* cp, double* tot_
           ll_encode(tot[k], ok ? seq : seq ^ 0x80000000u, w0, w1);  // a gather that timed out publishes nothing valid
           st_relaxed_sys_v2_u64(dst + 2 * k, w0, w1);
         }
+      }
+      if (lane == 0) {  // "the gather of this rank is over": the other CTAs may start polling their slots
+        unsigned long long w0, w1;
+        ll_encode(0.0, seq, w0, w1);
+        st_relaxed_gpu_v2_u64(res, w0, w1);
       }
       double r[NV];
 #pragma unroll

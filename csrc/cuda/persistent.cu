@@ -184,7 +184,7 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     for (int i = threadIdx.x; i < (int)(sizeof(RankCtx) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
   }
   __syncthreads();
-  star_pair_init(pair_mode);
+  star_pair_init(pair_mode & 1);
   unsigned int seq = c.ctl->red_seq, arrive_target = 0;
   const unsigned int hseq = c.ctl->halo_seq;
   const unsigned long long wd_limit = c.ctl->watchdog_ns ? c.ctl->watchdog_ns : kDefaultWatchdogNs;
@@ -259,8 +259,8 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     double v[2] = {threadIdx.x == 0 ? 1.0 : 0.0, 0.0};
     ++seq;
     arrive_target += ncta;
-    const RedResult rr = mode == 5 ? star_sum<2, true>(c, v, seq, cta, ncta, wd_limit, s_red, tr, pair_mode)
-                         : mode >= 3 ? star_sum<2>(c, v, seq, cta, ncta, wd_limit, s_red, nullptr, pair_mode)
+    const RedResult rr = mode == 5 ? star_sum<2, true>(c, v, seq, cta, ncta, wd_limit, s_red, tr, pair_mode & 1)
+                         : mode >= 3 ? star_sum<2>(c, v, seq, cta, ncta, wd_limit, s_red, nullptr, pair_mode & 1)
                                    : cross_rank_sum<2>(c, v, seq, arrive_target, cta, ncta, s_red, mode == 1 && has_nbr,
                                                        mode == 1 && c.sys_scope != 0);
     ok = rr.ok;
@@ -280,7 +280,7 @@ xgpu_bench_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int iters
     double* mine = reinterpret_cast<double*>(reinterpret_cast<char*>(c.ctl) + kCtaTimesOffset) + kCtaTimeWords * cta;
     for (int i = 0; i < 8; ++i) mine[i] = (double)tr[i] / (double)max(1, iters);
   }
-  star_pair_exit(pair_mode);
+  star_pair_exit(pair_mode & 1);
   if (cta == 0 && threadIdx.x == 0) {
     c.ctl->t_total = globaltimer_ns() - t0;
     c.ctl->red_seq = seq;
@@ -308,7 +308,8 @@ cudaError_t launch_xgpu_bench(const RankCtx* d_ctxs, int nvirt, int ctas_per_ran
 cudaError_t launch_cooperative_pairs(const void* fn, int nvirt, int ctas_per_rank, int threads, void** args, int* pair_arg,
                                      size_t smem, cudaStream_t stream) {
   static const bool enabled = std::getenv("PB_CLUSTERS") != nullptr;
-  *pair_arg = 0;
+  static const int star_everywhere = std::getenv("PB_MULTIRANK_STAR") != nullptr ? 2 : 0;  // A/B switch, bit 1 of the flag
+  *pair_arg = star_everywhere;
   if (enabled && ctas_per_rank >= 2 && (ctas_per_rank & 1) == 0) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(nvirt * ctas_per_rank);
@@ -322,11 +323,11 @@ cudaError_t launch_cooperative_pairs(const void* fn, int nvirt, int ctas_per_ran
     attr[1].val.clusterDim.x = 2, attr[1].val.clusterDim.y = 1, attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    *pair_arg = 1;
+    *pair_arg = 1 | star_everywhere;
     const cudaError_t e = cudaLaunchKernelExC(&cfg, fn, args);
     if (e == cudaSuccess) return e;
     cudaGetLastError();  // refused (e.g. not all clusters co-resident): fall back to single CTAs
-    *pair_arg = 0;
+    *pair_arg = star_everywhere;
   }
   return cudaLaunchCooperativeKernel(fn, dim3(nvirt * ctas_per_rank), dim3(threads), args, smem, stream);
 }

@@ -123,7 +123,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     mbar_fence_init();
   }
   __syncthreads();
-  star_pair_init(pair_mode);  // clusters of two CTAs: the partner's mbarrier exists from here on
+  star_pair_init(pair_mode & 1);  // clusters of two CTAs: the partner's mbarrier exists from here on
   // s_dyn is declared __align__(128); deriving every stage pointer from it by plain pointer arithmetic keeps
   // the accesses in the shared address space (LDS/STS instead of generic LD/ST)
   unsigned char* const stage_base = s_dyn;
@@ -153,11 +153,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // that wait for the other ranks' records poll their slot lines with nranks lanes each, and CTA 0's gather loop of the
   // star has to share the L2 with that traffic, while an elected last arriver reads the partials just once.
   unsigned int arrive_target = 0;
-  const bool multi_rank = c.nranks > 1;
+  const bool multi_rank = c.nranks > 1 && !(pair_mode & 2);  // (bit 1 of pair_mode: the star for several ranks too, A/B switch)
 #define PB_RED_PRE arrive_target += ncta;
 #define PB_RED(nv)                                                                                      \
   (multi_rank ? cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false)            \
-              : star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode))
+              : star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode & 1))
 #endif
   const double delta = ctl->delta;
   const long long max_iter = ctl->max_iter;
@@ -499,7 +499,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         ctl->status = PB_STATUS_WATCHDOG;
         ctl->red_seq = seq;
       }
-      star_pair_exit(pair_mode);
+      star_pair_exit(pair_mode & 1);
       return;
     }
     zr_old = rr.v[0] * h1h2;
@@ -891,7 +891,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     ctl->t_total = globaltimer_ns() - t_start;
     ctl->t_halo = s_t_halo;
   }
-  star_pair_exit(pair_mode);
+  star_pair_exit(pair_mode & 1);
 #undef PB_STAMP
 #undef PB_RED
 #undef PB_RED_PRE

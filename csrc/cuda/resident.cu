@@ -54,7 +54,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     s_wd_limit = wd ? wd : kDefaultWatchdogNs;
   }
   __syncthreads();
-  star_pair_init(pair_mode);
+  star_pair_init(pair_mode & 1);
   Control* ctl = c.ctl;
   const int S = c.pitch;
   const int sy = 1 << sy_log2, PP = sy + 2;
@@ -83,10 +83,10 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
   const double diag_out = diag_from_faces(c.g, inv_eps, inv_eps, inv_eps, inv_eps);
   unsigned int seq = ctl->red_seq, arrive_target = 0;
   const unsigned int hseq = ctl->halo_seq;
-  const bool multi_rank = c.nranks > 1;  // several ranks: cross_rank_sum measured faster than the star (persistent_tma.cu)
+  const bool multi_rank = c.nranks > 1 && !(pair_mode & 2);  // several ranks: cross_rank_sum measured faster than the star (persistent_tma.cu)
 #define PB_RES_RED(nv)                                                                                          \
   (arrive_target += ncta, multi_rank ? cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false) \
-                                     : star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode))
+                                     : star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode & 1))
 
   // ---- coefficient class of the sub-block and its ring (corners excluded): 0 inside, 1 outside, 2 mixed ----
   int mode;
@@ -183,7 +183,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
         ctl->status = PB_STATUS_WATCHDOG;
         ctl->red_seq = seq;
       }
-      star_pair_exit(pair_mode);
+      star_pair_exit(pair_mode & 1);
       return;
     }
     zr_old = rr.v[0] * h1h2;
@@ -375,7 +375,7 @@ pcg_resident_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, int sx,
     ctl->t_total = globaltimer_ns() - t_start;
     ctl->t_halo = t_halo;
   }
-  star_pair_exit(pair_mode);
+  star_pair_exit(pair_mode & 1);
 #undef PB_RES_RED
 #undef PB_STAMP
 }
