@@ -233,7 +233,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       return m0 | (m1 << 2) | (second ? 16 : 0) | (tall ? 32 : 0) | (full0 ? 64 : 0) | (full1 ? 128 : 0);
     };
     // items of a super-tile, appended by `writer` (one thread); returns how many
-    auto emit = [&](int li0, int lj0, int code, int at, bool writer) -> int {
+    // `part`: 0 the whole super-tile, 1 / 2 only its first / second half (a tall super-tile cut in two by the balancer)
+    auto emit = [&](int li0, int lj0, int code, int at, bool writer, int part) -> int {
       const int m0 = code & 3, m1 = (code >> 2) & 3;
       auto put = [&](int k, int li, int flags) {
         if (writer && k < kMaxItems) {
@@ -241,6 +242,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           s_items[k].flags = (unsigned char)flags, s_items[k].pad = 0;
         }
       };
+      if (part != 0) {  // halves of a tall super-tile: full tiles, constant coefficients, Ap recomputed
+        put(at, part == 1 ? li0 : li0 + TX, m0 | kItemRecomp);
+        return 1;
+      }
       if (code & 32) {
         put(at, li0, m0 | kItemRecomp | kItemTall);
         return 1;
@@ -266,7 +271,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       if (balance) {
         if (threadIdx.x == 0) tcode[t] = (unsigned char)code;
       } else {
-        nmine += emit(li0, lj0, code, nmine, threadIdx.x == 0);
+        nmine += emit(li0, lj0, code, nmine, threadIdx.x == 0, 0);
       }
     }
     if (balance) {
@@ -281,23 +286,44 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         int* load = reinterpret_cast<int*>(s_dyn);  // the stage memory is free until the first load is issued
         for (int i = lane; i < ncta; i += 32) load[i] = 0;
         __syncwarp();
-        int mine = 0;
-        int chunk = 0;  // codes of super-tiles t0 .. t0 + 31, one per lane
-        for (int t = 0; t < ntiles; ++t) {
-          if ((t & 31) == 0) chunk = t + lane < ntiles ? (int)__ldcg(tcode + t + lane) : 0;
-          const int code = __shfl_sync(0xffffffffu, chunk, t & 31);
-          int best = 0x7fffffff;  // key = cost so far * 1024 + CTA: the minimum is unique
+        // the CTA with the least cost so far (key = cost * 1024 + CTA: the minimum is unique)
+        auto least_loaded = [&]() -> int {
+          int best = 0x7fffffff;
           for (int i = lane; i < ncta; i += 32) best = min(best, load[i] * 1024 + i);
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
-          const int who = best & 1023;
-          if (lane == 0) load[who] += cost(code);
-          if (who == cta) {
-            int li0, lj0;
-            origin(t, li0, lj0);
-            mine += emit(li0, lj0, code, mine, lane == 0);
-          }
+          return best & 1023;
+        };
+        auto charge = [&](int who, int add) {
+          if (lane == 0) load[who] += add;
           __syncwarp();
+        };
+        // Even share of the total cost.  A tall item that would take its CTA more than a third of an item above that
+        // share is cut into its two 32-row halves, which go to the least loaded CTAs separately: with few super-tiles
+        // per CTA (the blocks of a multi-GPU run: 512 on 148 CTAs at 4096^2 on 8 GPUs) that is the difference between
+        // "4 tall items against 3" and "3 tall items + one half everywhere".
+        int total = 0, chunk = 0;  // chunk: codes of super-tiles t0 .. t0 + 31, one per lane
+        for (int t0 = 0; t0 < ntiles; t0 += 32) total += t0 + lane < ntiles ? cost((int)__ldcg(tcode + t0 + lane)) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        const int share = (total + ncta - 1) / ncta;
+        int mine = 0;
+        for (int t = 0; t < ntiles; ++t) {
+          if ((t & 31) == 0) chunk = t + lane < ntiles ? (int)__ldcg(tcode + t + lane) : 0;
+          const int code = __shfl_sync(0xffffffffu, chunk, t & 31);
+          int li0, lj0;
+          origin(t, li0, lj0);
+          int who = least_loaded();
+          if ((code & 32) && load[who] + 63 > share + 21) {
+            charge(who, 41);
+            if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 1);
+            who = least_loaded();
+            charge(who, 41);
+            if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 2);
+          } else {
+            charge(who, cost(code));
+            if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 0);
+          }
         }
         if (lane == 0) s_nmine = mine;
       }
