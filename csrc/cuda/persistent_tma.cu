@@ -96,7 +96,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   __shared__ RankCtx c;
   __shared__ double s_red[80];
   __shared__ __align__(8) uint64_t s_bar[S];
-  __shared__ TileItem s_items[kMaxItems];
+  __shared__ TileItem s_items[kMaxItems];    // work items of phase AB
+  __shared__ TileItem s_items_c[kMaxItems];  // work items of phase C: the same nodes; a tall item whose Ap is stored, not
+                                             // recomputed, appears as its two 32-row halves here (a tall phase-C stage
+                                             // has no room for p and Ap boxes)
   __shared__ int s_filled[S];  // per stage: ring cells were unpacked for the tile in flight (thread 0 only)
   __shared__ volatile int s_abort;  // some thread's TMA wait timed out; read after a barrier, so CTA-uniform
   __shared__ unsigned long long s_wd_limit;  // device-side wait limit in ns (kept out of the registers)
@@ -133,7 +136,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const CUtensorMap* maps_tall = reinterpret_cast<const CUtensorMap*>(c.tmaps) + kTallVariant * kMapsPerVariant;
   // The block is cut into "super-tiles" of srows x TY nodes, srows = 2 TX when tall items are allowed, else TX;
   // super-tile t belongs to CTA t mod ncta in both phases.
-  const bool tall_ok = Cfg::kTall && tall_mode != 0 && recompute_ap != 0;
+  const bool tall_ok = Cfg::kTall && tall_mode != 0;
   const int srows = tall_ok ? 2 * TX : TX;
   const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + srows - 1) / srows;
   const int ntiles = tiles_x * tiles_y;
@@ -242,12 +245,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           s_items[k].flags = (unsigned char)flags, s_items[k].pad = 0;
         }
       };
-      if (part != 0) {  // halves of a tall super-tile: full tiles, constant coefficients, Ap recomputed
-        put(at, part == 1 ? li0 : li0 + TX, m0 | kItemRecomp);
+      if (part != 0) {  // halves of a tall super-tile: full tiles, constant coefficients
+        put(at, part == 1 ? li0 : li0 + TX, m0 | (recompute_ap ? kItemRecomp : 0));
         return 1;
       }
       if (code & 32) {
-        put(at, li0, m0 | kItemRecomp | kItemTall);
+        put(at, li0, m0 | (recompute_ap ? kItemRecomp : 0) | kItemTall);
         return 1;
       }
       put(at, li0, m0 | ((recompute_ap && m0 != 2 && (code & 64)) ? kItemRecomp : 0));
@@ -333,7 +336,25 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     nmine = min(nmine, kMaxItems);  // the host sizes the launch so that this never cuts anything off
     __syncthreads();
   }
-  const int npre = min(S - 1, nmine);  // items of a phase that are issued ahead of the phase
+  // phase-C list (every thread counts, thread 0 writes)
+  int nmine_c = 0;
+  for (int j = 0; j < nmine; ++j) {
+    const TileItem it = s_items[j];
+    const bool split = (it.flags & kItemTall) && !(it.flags & kItemRecomp);
+    if (threadIdx.x == 0 && nmine_c + (split ? 2 : 1) <= kMaxItems) {
+      s_items_c[nmine_c] = it;
+      if (split) {
+        s_items_c[nmine_c].flags = it.flags & 3;
+        s_items_c[nmine_c + 1] = s_items_c[nmine_c];
+        s_items_c[nmine_c + 1].li0 = (unsigned short)(it.li0 + TX);
+      }
+    }
+    nmine_c += split ? 2 : 1;
+  }
+  nmine_c = min(nmine_c, kMaxItems);
+  __syncthreads();
+  const int npre = min(S - 1, nmine);      // items of phase AB that are issued ahead of the phase
+  const int npre_c = min(S - 1, nmine_c);  // the same for phase C
   auto item_rows = [&](int flags) -> int { return (flags & kItemTall) ? 2 * TX : TX; };
 
   // Halo rows travel as LL records (payload32 | sequence32 word pairs, see ctx.h): the producer needs no fence and
@@ -433,7 +454,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   // were written by other CTAs during phase AB, so that box has to wait for the reduction after it.
   auto issue_c_part = [&](int j, unsigned int st, int pbuf, bool part1, bool part2) {
     if (threadIdx.x == 0) {
-      const TileItem it = s_items[j];
+      const TileItem it = s_items_c[j];
       const int li0 = it.li0, lj0 = it.lj0;
       unsigned char* sb = stage_base + (size_t)st * Cfg::kStageBytes;
       uint64_t* bar = &s_bar[st];
@@ -677,7 +698,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     // the p_new box with ring of a tile that recomputes Ap (part 2, issued right after the reduction).
     const unsigned int c_pre_base = n_issued;
     if (threadIdx.x == 0) fence_proxy_async();  // our generic-proxy global stores -> TMA reads
-    for (int j = 0; j < npre; ++j) {
+    for (int j = 0; j < npre_c; ++j) {
       issue_c_part(j, n_issued % S, cur ^ 1, true, false);
       ++n_issued;
     }
@@ -692,7 +713,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       // of these stages are already armed for the bytes)
       if (recompute_ap) {
         if (threadIdx.x == 0) fence_proxy_async();
-        for (int j = 0; j < npre; ++j) issue_c_part(j, (c_pre_base + j) % S, cur ^ 1, false, true);
+        for (int j = 0; j < npre_c; ++j) issue_c_part(j, (c_pre_base + j) % S, cur ^ 1, false, true);
       }
       if (!rr.ok) {
         status = PB_STATUS_WATCHDOG;
@@ -707,10 +728,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
     alpha = zr_old / denom;
     // ======================= phase C =======================
     double acc_d = 0.0, acc_zr = 0.0;
-    for (int j = 0; j < nmine; ++j) {
-      if (j + S - 1 < nmine) issue_c(j + S - 1, cur ^ 1);
+    for (int j = 0; j < nmine_c; ++j) {
+      if (j + S - 1 < nmine_c) issue_c(j + S - 1, cur ^ 1);
       unsigned char* sb = wait_stage();
-      const TileItem item = s_items[j];  // CTA-uniform
+      const TileItem item = s_items_c[j];  // CTA-uniform
       const int li0 = item.li0, lj0 = item.lj0, tmode = item.flags & 3;
       const bool tall = (item.flags & kItemTall) != 0;
       const int rows = tall ? 2 * TX : TX;
@@ -833,7 +854,7 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         run_tile(std::true_type{});
       else
         run_tile(std::false_type{});
-      if (j == nmine - 1) fence_proxy_async_global();  // as in phase AB: w, r before the TMA reads of the next phase
+      if (j == nmine_c - 1) fence_proxy_async_global();  // as in phase AB: w, r before the TMA reads of the next phase
       __syncthreads();  // stage free
       ++n_consumed;
     }
@@ -950,12 +971,12 @@ static cudaError_t launch_div(const RankCtx* d_ctxs, int nvirt, int ctas_per_ran
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
                                   int l2_hints, bool compressed, bool recompute_ap, bool balance, cudaStream_t stream) {
   const int ra = (compressed && recompute_ap) ? 1 : 0, bal = balance ? 1 : 0;  // without coefficient classes no tile is known to be constant
-  // tile_rows: 16, 32, or 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into tall items
-  // (needs the recomputed Ap: a tall phase-C stage has no room for p and Ap boxes)
+  // tile_rows: 16, 32, or 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into tall items (in
+  // both phases when Ap is recomputed, in phase AB only when it is stored)
   if (tile_rows == 16)
     return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, bal, stream)
                       : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, 0, stream);
-  const int tall = (tile_rows == 64 && ra) ? 1 : 0;
+  const int tall = tile_rows == 64 ? 1 : 0;
   return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, tall, bal, stream)
                     : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, 0, 0, stream);
 }

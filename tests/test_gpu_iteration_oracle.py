@@ -78,7 +78,7 @@ def _close(got, ref, what):
 
 @pytest.mark.parametrize("iters", [1, 2])
 @pytest.mark.parametrize("pg", [(1, 1), (2, 2)])
-@pytest.mark.parametrize("tile_rows,ap_mode", [(32, 1), (32, 2), (16, 1), (64, 2)])
+@pytest.mark.parametrize("tile_rows,ap_mode", [(32, 1), (32, 2), (16, 1), (64, 2), (64, 1)])
 def test_first_iterations_against_pytorch(iters, pg, tile_rows, ap_mode):
     M, N = 400, 600
     w_ref, r_ref, p_ref, Ap_ref = _torch_pcg(M, N, iters)
