@@ -8,6 +8,17 @@ cd "$(dirname "$0")/../.."
 OUT=gpurun_out/campaign_$N; mkdir -p $OUT
 if [ "$N" = 1 ]; then TR="python"; else TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541"; fi
 nvidia-smi --query-gpu=index,name,clocks.max.sm,power.limit --format=csv,noheader > $OUT/gpus.txt
+# the box's peer-to-peer matrix as CUDA reports it, and the process grid derived from it
+python - $N > $OUT/p2p_topology.json 2>/dev/null <<'PY'
+import json, sys
+sys.path.insert(0, ".")
+from poisson_ellipse_openmp_mpi_cuda_b200.parallel.topology import grid_from_topology, probe_p2p
+n = int(sys.argv[1])
+m = probe_p2p(range(n))
+px, py, order, kind = grid_from_topology(m["perf"], 4096)
+print(json.dumps({"n_gpus": n, "performance_rank": m["perf"], "access": m["access"], "native_atomics": m["atomics"],
+                  "grid_for_4096": [px, py], "device_of_rank": order, "kind": kind}))
+PY
 # QUICK=1: our arm and the CLI only (a re-measurement after a kernel change)
 if [ "$N" != 1 ] && [ -z "$QUICK" ]; then timeout 600 python -m pytest tests/test_multi_gpu.py -m gpu -x -q > $OUT/pytest_multi_gpu.log 2>&1; tail -2 $OUT/pytest_multi_gpu.log; fi
 timeout 300 $TR bench.py --gpus $N --steps $STEPS --warmup 3 > $OUT/bench_ours_4096.json 2> $OUT/bench_ours_4096.err
