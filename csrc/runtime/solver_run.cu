@@ -81,14 +81,16 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
     // Tile height: 16 and 32 as asked; 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into
     // tall items, which halves the fixed cost per tile of a phase: in both phases when Ap is recomputed, in phase AB
     // only when it is stored (a tall phase-C stage has no room for p and Ap boxes; phase C then works on the two
-    // halves).  Auto (0) takes 64 when every CTA gets at least four (Ap stored: three) 64-row super-tiles -- the
+    // halves).  Auto (0) takes 64 when Ap is recomputed and every CTA gets at least four 64-row super-tiles -- the
     // balancer cuts tall items in two where a whole one would overshoot a CTA's share -- else 32.  Measured: the
-    // 4-GPU block of 4096^2 (1024 x 4096, 6.9 super-tiles per CTA) 62.0 against 64.9 us per iteration.
+    // 4-GPU block of 4096^2 (1024 x 4096, 6.9 super-tiles per CTA) 62.0 against 64.9 us per iteration; with stored Ap
+    // (L2-resident blocks) tall items in phase AB alone gain nothing (512 x 4096: 34.8 against 34.9 us on one GPU,
+    // 41.6 against 40.0 us in the 8-GPU run), so they are only taken on request there.
     const bool recompute = ap_recompute(opt.ap_mode) && opt.compressed != 0;
     long long super = 0;
     for (const RankCtx& c : hctx_) super = std::max<long long>(super, (long long)((c.nx + 63) / 64) * ((c.ny + kTileY - 1) / kTileY));
     int tile_rows = opt.tile_rows == 16 ? 16 : (opt.tile_rows == 64 ? 64 : 32);
-    if (opt.tile_rows == 0 && opt.compressed != 0 && super >= (recompute ? 4LL : 3LL) * ctas) tile_rows = 64;
+    if (opt.tile_rows == 0 && recompute && super >= 4LL * ctas) tile_rows = 64;
     const long long per_cta = (max_tiles * (tile_rows == 16 ? 2 : 1) + ctas - 1) / ctas;
     if (per_cta > persistent_tma_max_items())
       throw std::runtime_error("block too large for one GPU: " + std::to_string(per_cta) + " tiles per CTA, the persistent "
