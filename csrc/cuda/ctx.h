@@ -36,11 +36,7 @@ constexpr size_t kLl1Offset = 147456;              // [kRedValues][kMaxCtas][2] 
 constexpr size_t kResOffset = 180224;              // [kRedValues][2] u64: result record of star_sum (CTA 0 -> every CTA)
 constexpr size_t kTileCodeOffset = 180352;         // one code byte per super-tile (TMA kernel, cost-balanced tile assignment)
 constexpr int kTileCodeBytes = 16256;              // up to the end of the header
-#ifdef PB_VAR_HDR  // experiment only: the round-1 position of the arrays (star_sum's areas then overlap the first array)
-constexpr size_t kHeaderBytes = 131072;
-#else
 constexpr size_t kHeaderBytes = 196608;            // arrays start here; r is the first array
-#endif
 
 // Scalars of the iteration, status and device-side timers.  Lives at the start of the arena.
 struct Control {

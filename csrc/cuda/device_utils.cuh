@@ -414,11 +414,7 @@ __device__ __forceinline__ void star_pair_send(const double (&tot)[NV]) {
   for (int k = 0; k < NV; ++k) st_async_cluster_b64(rvals + 8u * k, (unsigned long long)__double_as_longlong(tot[k]), rbar);
 }
 
-#ifdef PB_VAR_NOINLINE  // experiment only
-#define PB_EXCHANGE_INLINE __noinline__
-#else
 #define PB_EXCHANGE_INLINE __forceinline__
-#endif
 
 // Staging area of CTA 0's gather: the records travel global -> shared memory with cp.async (L2 only, no register
 // per load in flight), kGatherSlots records per value.  One instance per kernel.

@@ -146,11 +146,6 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const int S_pitch = c.pitch;
 
   unsigned int seq = ctl->red_seq;
-#ifdef PB_VAR_OLDRED  // experiment only: the counter + aggregator reduction of the plain-load kernel
-  unsigned int arrive_target = 0;
-#define PB_RED_PRE arrive_target += ncta;
-#define PB_RED(nv) cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false)
-#else
   // One rank: the record star (3.3-3.6 us against 4.2-4.4 us).  Several ranks: the counter + elected aggregator of
   // cross_rank_sum, which measured faster there (2 GPUs: 5.3 against 5.6 us, 8 GPUs: 6.4 against 9.6 us): the CTAs
   // that wait for the other ranks' records poll their slot lines with nranks lanes each, and CTA 0's gather loop of the
@@ -161,7 +156,6 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
 #define PB_RED(nv)                                                                                      \
   (multi_rank ? cross_rank_sum<nv>(c, v, seq, arrive_target, cta, ncta, s_red, false, false)            \
               : star_sum<nv>(c, v, seq, cta, ncta, s_wd_limit, s_red, nullptr, pair_mode & 1))
-#endif
   const double delta = ctl->delta;
   const long long max_iter = ctl->max_iter;
   const int norm = ctl->norm;

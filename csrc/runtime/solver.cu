@@ -18,12 +18,10 @@ static_assert(offsetof(Control, watchdog_ns) - offsetof(Control, delta) == offse
 static_assert(sizeof(Control) <= kSlotsOffset, "Control overflows its page");
 static_assert(2 * kMaxRanks * kSlotWords * 8 <= kArriveOffset - kSlotsOffset, "slot area overflows");
 static_assert(kPartialsOffset + kMaxCtas * kPartialStride * 8 <= kCtaTimesOffset, "partials overflow");
-#ifndef PB_VAR_HDR
 static_assert(kCtaTimesOffset + kMaxCtas * kCtaTimeWords * 8 <= kLl1Offset, "per-CTA report area overflows");
 static_assert(kLl1Offset + kRedValues * kMaxCtas * 16 <= kResOffset, "star_sum CTA records overflow");
 static_assert(kResOffset + kRedValues * 16 <= kTileCodeOffset, "star_sum result record overflows");
 static_assert(kTileCodeOffset + kTileCodeBytes <= kHeaderBytes, "tile codes overflow");
-#endif
 static_assert(kHeaderBytes % 4096 == 0, "arrays must start page-aligned (TMA base alignment)");
 
 Solver::Solver(int M, int N, int Px, int Py, int first_rank, int nlocal, int device)
