@@ -91,6 +91,7 @@ int pb_solver_solve(pb_solver* s, const pb_solve_options* o, void* stream, pb_st
     opt.compressed = o->full_coefficients ? 0 : 1;
     opt.ap_mode = o->ap_mode;
     opt.no_balance = o->no_balance;
+    opt.ab_mode = o->ab_mode;
     opt.watchdog_s = o->watchdog_s;
     s->impl.solve(opt, as_stream(stream), stats);
   });
@@ -178,6 +179,7 @@ int pb_group_solve(pb_group* g, const pb_solve_options* o, pb_stats* stats) {
     opt.compressed = o->full_coefficients ? 0 : 1;
     opt.ap_mode = o->ap_mode;
     opt.no_balance = o->no_balance;
+    opt.ab_mode = o->ab_mode;
     opt.watchdog_s = o->watchdog_s;
     g->impl.solve(opt, stats);
   });

@@ -31,7 +31,8 @@ cudaError_t launch_persistent(const RankCtx* d_ctxs, int nvirt, int ctas_per_ran
 // constant-coefficient tiles merged into tall items)
 int persistent_tma_max_items();  // work items one CTA can hold
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
-                                  int l2_hints, bool compressed, bool recompute_ap, bool balance, cudaStream_t stream);
+                                  int l2_hints, bool compressed, bool recompute_ap, bool balance, bool rows_ab,
+                                  cudaStream_t stream);
 cudaError_t launch_tma_probe(const void* dmaps, const void* hmaps, int idx, int mode, int x, int y, unsigned int nbytes,
                              double* out, int* out_status, cudaStream_t stream);
 bool build_tensor_maps(const RankCtx& h_ctx, int tile_rows, void* out12);

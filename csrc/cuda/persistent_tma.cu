@@ -136,7 +136,8 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
   const CUtensorMap* maps_tall = reinterpret_cast<const CUtensorMap*>(c.tmaps) + kTallVariant * kMapsPerVariant;
   // The block is cut into "super-tiles" of srows x TY nodes, srows = 2 TX when tall items are allowed, else TX;
   // super-tile t belongs to CTA t mod ncta in both phases.
-  const bool tall_ok = Cfg::kTall && tall_mode != 0;
+  const bool tall_ok = Cfg::kTall && (tall_mode & 1) != 0;
+  const bool rows_ab = TX == 32 && (tall_mode & 2) != 0;  // phase AB of full constant-coefficient items by warp-private rows
   const int srows = tall_ok ? 2 * TX : TX;
   const int tiles_y = (c.ny + TY - 1) / TY, tiles_x = (c.nx + srows - 1) / srows;
   const int ntiles = tiles_x * tiles_y;
@@ -673,7 +674,75 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           }
         }
       };
-      if (tmode != 2)
+      // The same on a full item with constant coefficients, without the barrier in the middle: warp w owns NR = rows / 16
+      // consecutive rows of the item and all of its 64 columns (two per lane).  Every lane evaluates p_new for its two
+      // columns on the warp's rows and on the row above and below them (in registers; the two extra rows are computed
+      // twice in the CTA, which costs two multiply-adds per node and saves the round trip of p_new through shared
+      // memory with the barrier behind it), gets the left / right neighbours from the adjacent lanes by shuffle (the
+      // outermost lanes evaluate the ring column), and goes straight on to the stencil.  Same expressions on the same
+      // operands as p_cell / ab_node: the same bits for p_new and Ap; only the order of the per-thread partial sums of
+      // (Ap, p) differs from the tile path.
+      auto run_rows = [&](auto nr_tag) {
+        constexpr int NR = decltype(nr_tag)::value;
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        const int row0 = 1 + warp * NR;  // first own row of the box in shared memory (row 0 is the ring)
+        const int ec = 2 * lane + 2;     // box column of the lane's first node (the box starts one column early)
+        double pn[NR + 2][2];
+#pragma unroll
+        for (int i = 0; i < NR + 2; ++i) {
+          const int e = (row0 - 1 + i) * EC + ec;
+          const double2 rr = *reinterpret_cast<const double2*>(s_r + e);
+          const double2 pp = *reinterpret_cast<const double2*>(s_p + e);
+          pn[i][0] = fma(beta, pp.x, div_known<DIV>(rr.x, dg, rc));
+          pn[i][1] = fma(beta, pp.y, div_known<DIV>(rr.y, dg, rc));
+        }
+        double edge[NR];  // lanes 0 / 31: p_new in the ring column left / right of the item, own rows
+#pragma unroll
+        for (int i = 0; i < NR; ++i) edge[i] = 0.0;
+        const bool outer = lane == 0 || lane == 31;
+        if (outer) {
+          const int ecol = lane == 0 ? 1 : EC - 2;
+#pragma unroll
+          for (int i = 0; i < NR; ++i) {
+            const int e = (row0 + i) * EC + ecol;
+            edge[i] = fma(beta, s_p[e], div_known<DIV>(s_r[e], dg, rc));
+          }
+        }
+        double* po = pout + (size_t)(li0 - 1 + row0) * S_pitch + (lj0 + 2 * lane + kColOff);
+        double* ap = c.Ap + (size_t)(li0 - 1 + row0) * S_pitch + (lj0 + 2 * lane + kColOff);
+#pragma unroll
+        for (int i = 0; i < NR; ++i) {
+          double left = __shfl_up_sync(0xffffffffu, pn[i + 1][1], 1);
+          double right = __shfl_down_sync(0xffffffffu, pn[i + 1][0], 1);
+          if (lane == 0) left = edge[i];
+          if (lane == 31) right = edge[i];
+          const double v0 = stencil_value<DIV>(K, pn[i + 1][0], pn[i][0], pn[i + 2][0], left, pn[i + 1][1], cf, cf, cf, cf);
+          const double v1 = stencil_value<DIV>(K, pn[i + 1][1], pn[i][1], pn[i + 2][1], pn[i + 1][0], right, cf, cf, cf, cf);
+          *reinterpret_cast<double2*>(po + (size_t)i * S_pitch) = make_double2(pn[i + 1][0], pn[i + 1][1]);
+          if (keep_ap) *reinterpret_cast<double2*>(ap + (size_t)i * S_pitch) = make_double2(v0, v1);
+          acc_ab = fma(v0, pn[i + 1][0], acc_ab);
+          acc_ab = fma(v1, pn[i + 1][1], acc_ab);
+        }
+        // ring cells of the whole block keep their p_new in global memory (the next phase AB reads them as p_old)
+        if (warp == 0 && li0 == 1)
+          *reinterpret_cast<double2*>(po - S_pitch) = make_double2(pn[0][0], pn[0][1]);
+        if (warp == kThreads / 32 - 1 && li0 + rows - 1 == c.nx)
+          *reinterpret_cast<double2*>(po + (size_t)NR * S_pitch) = make_double2(pn[NR + 1][0], pn[NR + 1][1]);
+        if (lane == 0 && lj0 == 1) {
+#pragma unroll
+          for (int i = 0; i < NR; ++i) po[(size_t)i * S_pitch - 1] = edge[i];
+        }
+        if (lane == 31 && lj0 + TY - 1 == c.ny) {
+#pragma unroll
+          for (int i = 0; i < NR; ++i) po[(size_t)i * S_pitch + 2] = edge[i];
+        }
+      };
+      if (rows_ab && full && tmode != 2) {
+        if (tall)
+          run_rows(std::integral_constant<int, 2 * TX / (kThreads / 32)>{});
+        else
+          run_rows(std::integral_constant<int, TX / (kThreads / 32)>{});
+      } else if (tmode != 2)
         run_tile(std::true_type{});
       else
         run_tile(std::false_type{});
@@ -963,14 +1032,15 @@ static cudaError_t launch_div(const RankCtx* d_ctxs, int nvirt, int ctas_per_ran
 }
 
 cudaError_t launch_persistent_tma(const RankCtx* d_ctxs, int nvirt, int ctas_per_rank, int tile_rows, int div,
-                                  int l2_hints, bool compressed, bool recompute_ap, bool balance, cudaStream_t stream) {
+                                  int l2_hints, bool compressed, bool recompute_ap, bool balance, bool rows_ab,
+                                  cudaStream_t stream) {
   const int ra = (compressed && recompute_ap) ? 1 : 0, bal = balance ? 1 : 0;  // without coefficient classes no tile is known to be constant
   // tile_rows: 16, 32, or 64 = 32-row tiles with pairs of full constant-coefficient tiles merged into tall items (in
   // both phases when Ap is recomputed, in phase AB only when it is stored)
   if (tile_rows == 16)
     return compressed ? launch_div<16, true>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, bal, stream)
                       : launch_div<16, false>(d_ctxs, nvirt, ctas_per_rank, 1, div, l2_hints, ra, 0, 0, stream);
-  const int tall = tile_rows == 64 ? 1 : 0;
+  const int tall = (tile_rows == 64 ? 1 : 0) | (rows_ab ? 2 : 0);  // bit 0: tall items, bit 1: phase AB by warp-private rows
   return compressed ? launch_div<32, true>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, tall, bal, stream)
                     : launch_div<32, false>(d_ctxs, nvirt, ctas_per_rank, 0, div, l2_hints, ra, 0, 0, stream);
 }

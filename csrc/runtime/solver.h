@@ -34,6 +34,7 @@ struct SolveOptions {
   int error_report = 1;
   int compressed = 1;       // TMA kernel: coefficient classes (1 byte/cell) instead of streaming a, b, D
   int no_balance = 0;       // TMA kernel: 1 = cyclic tile -> CTA map instead of the cost-balanced one
+  int ab_mode = 0;          // TMA kernel, phase AB of full constant-coefficient items: 0 = warp-private rows, 1 = tile path
   int ap_mode = 0;          // TMA kernel, uniform tiles: 1 store + reload Ap, 2 recompute it in phase C, 0 = default
   int l2_hints = 0;         // TMA loads carry L2 eviction priorities (helps ~2 % when the working set ~ L2 size)
   int tile_rows = 0;        // TMA persistent kernel: 32 (2 stages), 16 (4 stages), 64 (32 + tall items); 0 = auto

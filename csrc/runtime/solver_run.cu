@@ -97,8 +97,10 @@ void Solver::solve_persistent(const SolveOptions& opt, cudaStream_t stream) {
                                "kernel holds " + std::to_string(persistent_tma_max_items()) + "; use more GPUs");
     last_tile_rows_ = tile_rows;
     static const bool env_no_balance = std::getenv("PB_NO_BALANCE") != nullptr;  // A/B switch for measurements
+    const char* env_rows = std::getenv("PB_AB_ROWS");  // A/B switch for measurements (read per launch): "0" = tile path
+    const bool rows_ab = opt.ab_mode == 0 && !(env_rows && env_rows[0] == '0');
     PB_CUDA_CHECK(launch_persistent_tma(dctx_, nlocal(), ctas, tile_rows, exact, opt.l2_hints, opt.compressed != 0,
-                                        ap_recompute(opt.ap_mode), !(env_no_balance || opt.no_balance), stream));
+                                        ap_recompute(opt.ap_mode), !(env_no_balance || opt.no_balance), rows_ab, stream));
   } else
     PB_CUDA_CHECK(launch_persistent(dctx_, nlocal(), ctas, exact, stream));
   last_launches_ += 1;

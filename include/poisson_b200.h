@@ -147,6 +147,13 @@ typedef struct pb_solve_options {
   int no_balance;     /* TMA persistent kernel: 1 = tiles go to CTAs cyclically; 0 = cost-balanced assignment (the
                          default; the sums are then taken in a different order, so results differ in the last bits from
                          a cyclic run) */
+  int ab_mode;        /* TMA persistent kernel, phase AB on full tiles with constant coefficients.  0 (default): every
+                         warp owns whole rows of the tile, evaluates p_new for them and for the row above and below in
+                         registers and goes straight on to the stencil (no barrier between the two halves of the
+                         phase, no round trip of p_new through shared memory).  1: the tile path (p update in place in
+                         shared memory, barrier, stencil), which is what mixed and partial tiles always take.  Same
+                         bits for p_new and Ap either way; the order of the per-thread partial sums of (Ap, p)
+                         differs, so the two agree to rounding. */
 } pb_solve_options;
 
 int pb_cuda_device_count(void);

@@ -80,6 +80,7 @@ class SolveOptions(C.Structure):
         ("full_coefficients", C.c_int),
         ("ap_mode", C.c_int),
         ("no_balance", C.c_int),
+        ("ab_mode", C.c_int),
     ]
 
 

@@ -158,7 +158,8 @@ class GpuSolver:
     def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
               exact_div: bool | None = None, ctas_per_sm: int = 0, error_report: bool = True,
               watchdog_s: float = 0.0, tile_rows: int = 0, div: str = "markstein", l2_hints: bool = False,
-              full_coefficients: bool = False, ap_mode: int = 0, balance: bool = True, stream=None) -> dict:
+              full_coefficients: bool = False, ap_mode: int = 0, balance: bool = True, ab_rows: bool = True,
+              stream=None) -> dict:
         """``div``: how the stencil divides by h1/h2 -- "true" (IEEE division), "markstein" (three-instruction
         sequence with the same bits, default) or "recip" (multiply by the reciprocal).  ``exact_div`` is the
         older boolean spelling: True -> "true", False -> "recip"."""
@@ -168,7 +169,7 @@ class GpuSolver:
             div = "true" if exact_div else "recip"
         opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, DIVS[div], ctas_per_sm,
                                    int(error_report), tile_rows, watchdog_s, int(l2_hints), int(full_coefficients),
-                                   int(ap_mode), int(not balance))
+                                   int(ap_mode), int(not balance), int(not ab_rows))
         st = _native.Stats()
         with torch.cuda.device(self.device):
             _native.check(self.lib.pb_solver_solve(self._h, C.byref(opt), _stream_ptr(stream), C.byref(st)),
@@ -251,9 +252,10 @@ class GroupSolver:
 
     def solve(self, method: str = "persistent", norm: str = "weighted", delta: float = 1e-6, max_iter: int = -1,
               div: str = "markstein", watchdog_s: float = 0.0, tile_rows: int = 0, l2_hints: bool = False,
-              full_coefficients: bool = False, ap_mode: int = 0, balance: bool = True, **_ignored) -> dict:
+              full_coefficients: bool = False, ap_mode: int = 0, balance: bool = True, ab_rows: bool = True,
+              **_ignored) -> dict:
         opt = _native.SolveOptions(METHODS[method], NORMS[norm], delta, max_iter, DIVS[div], 0, 1, tile_rows, watchdog_s,
-                                   int(l2_hints), int(full_coefficients), int(ap_mode), int(not balance))
+                                   int(l2_hints), int(full_coefficients), int(ap_mode), int(not balance), int(not ab_rows))
         st = _native.Stats()
         _native.check(self.lib.pb_group_solve(self._h, C.byref(opt), C.byref(st)), "pb_group_solve")
         out = st.as_dict()

@@ -78,12 +78,14 @@ def _close(got, ref, what):
 
 @pytest.mark.parametrize("iters", [1, 2])
 @pytest.mark.parametrize("pg", [(1, 1), (2, 2)])
-@pytest.mark.parametrize("tile_rows,ap_mode", [(32, 1), (32, 2), (16, 1), (64, 2), (64, 1)])
-def test_first_iterations_against_pytorch(iters, pg, tile_rows, ap_mode):
+@pytest.mark.parametrize("tile_rows,ap_mode,ab_rows", [(32, 1, True), (32, 2, True), (16, 1, True), (64, 2, True), (64, 1, True),
+                                                       (32, 1, False), (64, 2, False)])
+def test_first_iterations_against_pytorch(iters, pg, tile_rows, ap_mode, ab_rows):
+    """ab_rows: phase AB of full constant-coefficient items by warp-private rows (the default) or on the tile path."""
     M, N = 400, 600
     w_ref, r_ref, p_ref, Ap_ref = _torch_pcg(M, N, iters)
     s = _solver(M, N, *pg)
-    res = s.solve(max_iter=iters, tile_rows=tile_rows, ap_mode=ap_mode, error_report=False)
+    res = s.solve(method="persistent_tma", max_iter=iters, tile_rows=tile_rows, ap_mode=ap_mode, ab_rows=ab_rows, error_report=False)
     assert res["iters"] == iters and res["status_name"] == "max_iter"
     pname = "p1" if iters % 2 else "p0"  # the buffer phase AB of the last iteration wrote
     for l in range(pg[0] * pg[1]):
@@ -144,6 +146,32 @@ def test_converged_solution_elementwise_against_cpu_oracle(native, tile_rows, ap
         w = s.solution_host()
         assert float((w - ref).abs().max()) < 1e-10
         s.close()
+
+
+@pytest.mark.parametrize("pg", [(1, 1), (2, 2), (1, 3)])
+@pytest.mark.parametrize("tile_rows", [32, 64])
+def test_phase_ab_by_rows_gives_the_bits_of_the_tile_path(pg, tile_rows):
+    """Phase AB by warp-private rows evaluates the same expressions on the same operands as the tile path: after one
+    iteration p_new (ring cells of the block included) and Ap are equal bit for bit; w and r carry alpha, whose
+    reduction sums the per-thread partials in another order, so they -- and the converged solutions -- agree to
+    rounding."""
+    M, N = 400, 600
+    s = _solver(M, N, *pg)
+    kw = dict(method="persistent_tma", tile_rows=tile_rows, ap_mode=1, error_report=False)
+    s.solve(max_iter=1, ab_rows=False, **kw)
+    ref = [{k: s.array(k, l).clone() for k in ("p1", "Ap", "w", "r")} for l in range(pg[0] * pg[1])]
+    s.solve(max_iter=1, ab_rows=True, **kw)
+    for l in range(pg[0] * pg[1]):
+        assert torch.equal(s.array("p1", l), ref[l]["p1"]), f"p_new block {l}"
+        assert torch.equal(s.array("Ap", l), ref[l]["Ap"]), f"Ap block {l}"
+        for k in ("w", "r"):
+            assert float((s.array(k, l) - ref[l][k]).abs().max()) <= 1e-13 * float(ref[l][k].abs().max()), k
+    ra = s.solve(ab_rows=False, **kw)
+    wa = s.solution_host().clone()
+    rb = s.solve(ab_rows=True, **kw)
+    assert ra["iters"] == rb["iters"] == 546
+    assert float((s.solution_host() - wa).abs().max()) < 1e-11
+    s.close()
 
 
 def test_tall_items_are_used_and_counted():
