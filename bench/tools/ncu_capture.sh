@@ -11,6 +11,9 @@ run() {  # name M N iterations [Px Py]
     -o gpurun_out/$name python bench/tools/ncu_target.py "$@" > gpurun_out/$name.log 2>&1
   echo "$name rc=$?"; tail -2 gpurun_out/$name.log
 }
-run ncu_tma_4096x4096_10it 4096 4096 10
-run ncu_tma_4096x512_20it 4096 512 20
-run ncu_tma_virtual2x1_4096x1024_10it 4096 1024 10 2 1
+# usage: ncu_capture.sh [suffix [only-first]]   (suffix goes into the report names, e.g. _rows)
+SUF=$1
+run ncu_tma_4096x4096_10it$SUF 4096 4096 10
+[ -n "$2" ] && exit 0
+run ncu_tma_4096x512_20it$SUF 4096 512 20
+run ncu_tma_virtual2x1_4096x1024_10it$SUF 4096 1024 10 2 1

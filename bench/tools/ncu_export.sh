@@ -4,10 +4,11 @@ cd "$(dirname "$0")/../.."
 mkdir -p profiles/r2/ncu
 for rep in gpurun_out/ncu_*.ncu-rep; do
   base=$(basename $rep .ncu-rep)
-  cp $rep profiles/r2/ncu/
-  ncu -i $rep --page raw --csv 2>/dev/null | python - "$base" <<'PY' > profiles/r2/ncu/$base.summary.txt
+  gzip -c $rep > profiles/r2/ncu/$base.ncu-rep.gz
+  ncu -i $rep --page raw --csv 2>/dev/null > /tmp/$base.raw.csv
+  python - /tmp/$base.raw.csv <<'PY' > profiles/r2/ncu/$base.summary.txt
 import csv, sys
-rows = list(csv.reader(sys.stdin))
+rows = list(csv.reader(open(sys.argv[1])))
 if len(rows) < 3:
     print("no data"); sys.exit(0)
 hdr, units, vals = rows[0], rows[1], rows[2]
@@ -20,7 +21,7 @@ want = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__
         "smsp__pcsamp_sample_buffer_total", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"]
 for w in want:
     for i, h in enumerate(hdr):
-        if h == w:
+        if h == w or h.endswith("." + w):
             print(f"{h} [{units[i]}] = {vals[i]}")
 PY
 done
