@@ -46,6 +46,7 @@ struct TileItem {
 };
 constexpr int kItemRecomp = 4, kItemTall = 8;
 constexpr int kTallVariant = 2;  // tensor-map set with boxes of 2 * 32 rows
+constexpr int kCostTall = 59, kCostHalf = 38;  // balancer: a tall item, a full 32-row item with recomputed Ap (0.1 us)
 
 template <int TX>
 struct TmaCfg {
@@ -254,10 +255,12 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       return 2;
     };
     // relative cost of a super-tile, phases AB + C, in 0.1 us (least-squares fit of the per-CTA busy times at 4096^2,
-    // bench/experiments/cta_balance.py: tall item 6.3 us, 32-row item with constant coefficients 4.1 us, mixed 4.9 us)
+    // 2048 x 4096 and 1024 x 4096 with phase AB by rows, bench/experiments/cta_balance.py: tall item 5.9 us, full 32-row
+    // item with constant coefficients and recomputed Ap 3.8 us, with stored Ap or partial 4.5 us, mixed 5.3 us)
+    auto half_cost = [&](int m, bool full_tile) -> int { return m == 2 ? 53 : ((recompute_ap && full_tile) ? kCostHalf : 45); };
     auto cost = [&](int code) -> int {
-      if (code & 32) return 63;
-      return ((code & 3) == 2 ? 49 : 41) + ((code & 16) ? (((code >> 2) & 3) == 2 ? 49 : 41) : 0);
+      if (code & 32) return kCostTall;
+      return half_cost(code & 3, (code & 64) != 0) + ((code & 16) ? half_cost((code >> 2) & 3, (code & 128) != 0) : 0);
     };
     unsigned char* tcode = reinterpret_cast<unsigned char*>(ctl) + kTileCodeOffset;
     const bool balance = CC && balance_mode != 0 && ncta > 1 && ntiles <= kTileCodeBytes;
@@ -312,11 +315,11 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
           int li0, lj0;
           origin(t, li0, lj0);
           int who = least_loaded();
-          if ((code & 32) && load[who] + 63 > share + 21) {
-            charge(who, 41);
+          if ((code & 32) && load[who] + kCostTall > share + kCostTall / 3) {
+            charge(who, recompute_ap ? kCostHalf : 45);
             if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 1);
             who = least_loaded();
-            charge(who, 41);
+            charge(who, recompute_ap ? kCostHalf : 45);
             if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 2);
           } else {
             charge(who, cost(code));

@@ -229,9 +229,10 @@ def test_recomputed_Ap_is_bit_identical_to_stored_Ap(pg, tile_rows):
     must give the same iteration count, the same stop norm and the same bits as ap_mode=1."""
     for grid in [(96, 200), (400, 600)]:
         s = _solver(*grid, *pg)
-        ra = s.solve(tile_rows=tile_rows, ap_mode=1)
+        # (cyclic tile -> CTA map for both: the balancer's costs depend on the Ap mode, and with the map the summation order)
+        ra = s.solve(tile_rows=tile_rows, ap_mode=1, balance=False)
         wa = s.solution_host().clone()
-        rb = s.solve(tile_rows=tile_rows, ap_mode=2)
+        rb = s.solve(tile_rows=tile_rows, ap_mode=2, balance=False)
         wb = s.solution_host()
         assert ra["iters"] == rb["iters"] and rb["status"] == 1
         assert ra["diff_norm"] == rb["diff_norm"]
