@@ -204,15 +204,18 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       const int in = __syncthreads_and(all_in ? 1 : 0), out = __syncthreads_and(all_out ? 1 : 0);
       return in ? 0 : (out ? 1 : 2);
     };
-    auto origin = [&](int t, int& li0, int& lj0) {
-      int tx = t / tiles_y;
-      const int ty = t - tx * tiles_y;
+    // first node of the super-tile in row tx, column ty of the sweep (sweep index t = tx * tiles_y + ty)
+    auto origin_at = [&](int tx, int ty, int& li0, int& lj0) {
       // Row order: first, last, second, ...: the tiles that store halo rows for the x-neighbours (phase C) and the
       // tiles that need the neighbours' rows (phase AB) then come first on both sides, so the NVLink latency of the
       // halo records hides behind the remaining tiles instead of sitting in front of a reduction.  (Enumerating the
       // whole perimeter first was measured 7 % slower per phase: it breaks the streaming order of the sweep.)
       if (has_nbr && tiles_x > 2) tx = tx == 0 ? 0 : (tx == 1 ? tiles_x - 1 : tx - 1);
       li0 = 1 + tx * srows, lj0 = 1 + ty * TY;
+    };
+    auto origin = [&](int t, int& li0, int& lj0) {
+      const int tx = t / tiles_y;
+      origin_at(tx, t - tx * tiles_y, li0, lj0);
     };
     // code of a super-tile: bits 0-1 class of the first half, 2-3 of the second, 4 second half exists, 5 tall,
     // 6 / 7 first / second half is a full tile
@@ -284,20 +287,45 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       }
       if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
+        // Cost so far per CTA.  Up to 160 CTAs (one GPU: 148) the costs of CTAs lane, lane + 32, ... live in this lane's
+        // registers and the minimum is one redux instruction; the walk over 4096 super-tiles is a serial chain, and
+        // with the table in shared memory (the fallback) it took 2.5 ms at the start of every 4096^2 solve.
+        const bool in_regs = ncta <= 160;
+        int ld0 = 0, ld1 = 0, ld2 = 0, ld3 = 0, ld4 = 0;
         int* load = reinterpret_cast<int*>(s_dyn);  // the stage memory is free until the first load is issued
-        for (int i = lane; i < ncta; i += 32) load[i] = 0;
-        __syncwarp();
-        // the CTA with the least cost so far (key = cost * 1024 + CTA: the minimum is unique)
-        auto least_loaded = [&]() -> int {
+        if (!in_regs) {
+          for (int i = lane; i < ncta; i += 32) load[i] = 0;
+          __syncwarp();
+        }
+        // the CTA with the least cost so far (key = cost * 1024 + CTA: the minimum is unique) and that cost
+        auto least_loaded = [&](int& cost_so_far) -> int {
           int best = 0x7fffffff;
-          for (int i = lane; i < ncta; i += 32) best = min(best, load[i] * 1024 + i);
+          if (in_regs) {
+            if (lane < ncta) best = ld0 * 1024 + lane;
+            if (lane + 32 < ncta) best = min(best, ld1 * 1024 + lane + 32);
+            if (lane + 64 < ncta) best = min(best, ld2 * 1024 + lane + 64);
+            if (lane + 96 < ncta) best = min(best, ld3 * 1024 + lane + 96);
+            if (lane + 128 < ncta) best = min(best, ld4 * 1024 + lane + 128);
+            best = __reduce_min_sync(0xffffffffu, best);
+          } else {
+            for (int i = lane; i < ncta; i += 32) best = min(best, load[i] * 1024 + i);
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+            for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+          }
+          cost_so_far = best >> 10;
           return best & 1023;
         };
         auto charge = [&](int who, int add) {
-          if (lane == 0) load[who] += add;
-          __syncwarp();
+          if (in_regs) {
+            ld0 += who == lane ? add : 0;
+            ld1 += who == lane + 32 ? add : 0;
+            ld2 += who == lane + 64 ? add : 0;
+            ld3 += who == lane + 96 ? add : 0;
+            ld4 += who == lane + 128 ? add : 0;
+          } else {
+            if (lane == 0) load[who] += add;
+            __syncwarp();
+          }
         };
         // Even share of the total cost.  A tall item that would take its CTA more than a third of an item above that
         // share is cut into its two 32-row halves, which go to the least loaded CTAs separately: with few super-tiles
@@ -309,16 +337,17 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
         for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
         const int share = (total + ncta - 1) / ncta;
         int mine = 0;
-        for (int t = 0; t < ntiles; ++t) {
+        for (int t = 0, tx = 0, ty = 0; t < ntiles; ++t) {
           if ((t & 31) == 0) chunk = t + lane < ntiles ? (int)__ldcg(tcode + t + lane) : 0;
           const int code = __shfl_sync(0xffffffffu, chunk, t & 31);
-          int li0, lj0;
-          origin(t, li0, lj0);
-          int who = least_loaded();
-          if ((code & 32) && load[who] + kCostTall > share + kCostTall / 3) {
+          int li0, lj0, sofar;
+          origin_at(tx, ty, li0, lj0);  // = origin(t), without the division
+          if (++ty == tiles_y) ty = 0, ++tx;
+          int who = least_loaded(sofar);
+          if ((code & 32) && sofar + kCostTall > share + kCostTall / 3) {
             charge(who, recompute_ap ? kCostHalf : 45);
             if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 1);
-            who = least_loaded();
+            who = least_loaded(sofar);
             charge(who, recompute_ap ? kCostHalf : 45);
             if (who == cta) mine += emit(li0, lj0, code, mine, lane == 0, 2);
           } else {
