@@ -174,6 +174,42 @@ def test_phase_ab_by_rows_gives_the_bits_of_the_tile_path(pg, tile_rows):
     s.close()
 
 
+@pytest.mark.parametrize("ab_rows", [True, False])
+@pytest.mark.parametrize("grid,pg", [((257, 193), (1, 1)), ((513, 385), (2, 2)), ((513, 193), (2, 1)), ((257, 385), (1, 2))])
+def test_blocks_whose_edges_are_full_tiles(grid, pg, ab_rows):
+    """Blocks of 256 x 192 nodes: every edge of the block is an edge of full 64 x 64 items, so the rows path stores the
+    block's ring cells of p_new from its own registers (top / bottom by the first / last warp, left / right by lanes
+    0 / 31) and the neighbours' halo rows meet full tiles.  Three iterations against PyTorch: the ring of p is read in
+    iterations 2 and 3."""
+    M, N = grid
+    for tile_rows in (64, 32):
+        for iters in (1, 3):
+            w_ref, r_ref, p_ref, _ = _torch_pcg(M, N, iters)
+            s = _solver(M, N, *pg)
+            res = s.solve(method="persistent_tma", max_iter=iters, tile_rows=tile_rows, ap_mode=2, ab_rows=ab_rows, error_report=False)
+            assert res["iters"] == iters
+            pname = "p1" if iters % 2 else "p0"
+            for l in range(pg[0] * pg[1]):
+                blk = s.block(l)
+                assert blk.nx == 256 and blk.ny == 192
+                I, J = slice(blk.i0, blk.i0 + blk.nx), slice(blk.j0, blk.j0 + blk.ny)
+                _close(s.interior("w", l), w_ref[I, J], f"w block {l}")
+                _close(s.interior("r", l), r_ref[I, J], f"r block {l}")
+                _close(s.interior(pname, l), p_ref[I, J], f"p block {l}")
+                # the ring of p next to a neighbour holds the neighbour's p (recomputed here from its r): compare it too
+                full = s.array(pname, l)
+                co = s.col_off
+                if blk.i0 > 1:
+                    _close(full[0, co + 1:co + 1 + blk.ny], p_ref[blk.i0 - 1, J], f"top ring of p, block {l}")
+                if blk.i0 + blk.nx < M:
+                    _close(full[blk.nx + 1, co + 1:co + 1 + blk.ny], p_ref[blk.i0 + blk.nx, J], f"bottom ring of p, block {l}")
+                if blk.j0 > 1:
+                    _close(full[1:blk.nx + 1, co], p_ref[I, blk.j0 - 1], f"left ring of p, block {l}")
+                if blk.j0 + blk.ny < N:
+                    _close(full[1:blk.nx + 1, co + 1 + blk.ny], p_ref[I, blk.j0 + blk.ny], f"right ring of p, block {l}")
+            s.close()
+
+
 def test_tall_items_are_used_and_counted():
     """tile_rows=64 merges pairs of full constant-coefficient tiles; the kernel's own tile counts must still add up to
     the number of 32 x 64 tiles of the block, and the result must agree with 32-row tiles to rounding."""
