@@ -162,7 +162,14 @@ class GpuSolver:
               stream=None) -> dict:
         """``div``: how the stencil divides by h1/h2 -- "true" (IEEE division), "markstein" (three-instruction
         sequence with the same bits, default) or "recip" (multiply by the reciprocal).  ``exact_div`` is the
-        older boolean spelling: True -> "true", False -> "recip"."""
+        older boolean spelling: True -> "true", False -> "recip".
+
+        TMA kernel only (see ``pb_solve_options`` in include/poisson_b200.h): ``tile_rows`` 0 = auto, 16 / 32 / 64;
+        ``ap_mode`` 0 = auto, 1 = Ap stored, 2 = recomputed in phase C; ``balance`` False = cyclic tile -> CTA map
+        instead of the cost-balanced one; ``ab_rows`` False = phase AB on the tile path for every tile instead of
+        warp-private rows on full constant-coefficient tiles; ``full_coefficients`` streams a, b, D instead of the
+        class bytes; ``l2_hints`` puts eviction priorities on the TMA loads.  All of them leave every value equal to
+        rounding; ``balance`` and ``ab_rows`` change the order of the partial sums."""
         if not self._finalized:
             self.finalize()
         if exact_div is not None:
