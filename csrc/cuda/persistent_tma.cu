@@ -716,6 +716,10 @@ pcg_persistent_tma_kernel(const RankCtx* __restrict__ ctxs, int ctas_per_rank, i
       // (Ap, p) differs from the tile path.
       auto run_rows = [&](auto nr_tag) {
         constexpr int NR = decltype(nr_tag)::value;
+        // 16-byte accesses: a lane's two nodes start at an even column of the box in shared memory and at an even
+        // column of the padded row in global memory (lj0 is odd, kColOff is odd, the pitch is a multiple of 16 doubles)
+        static_assert(EC % 2 == 0 && TY % 2 == 0 && kColOff % 2 == 1, "rows path: pairs of nodes must be 16-byte aligned");
+        static_assert(NR * (kThreads / 32) == TX || NR * (kThreads / 32) == 2 * TX, "rows path: the warps' rows must tile the item");
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
         const int row0 = 1 + warp * NR;  // first own row of the box in shared memory (row 0 is the ring)
         const int ec = 2 * lane + 2;     // box column of the lane's first node (the box starts one column early)
