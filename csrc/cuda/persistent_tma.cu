@@ -23,6 +23,13 @@
 // the ellipse or touching the boundary of Omega; those keep the full fp64 boxes.  Values are selected, never
 // recomputed, so the results are bit-identical to streaming the coefficient arrays (tests compare them).
 //
+// Work items and who computes what: the block is cut into super-tiles of 64 x 64 nodes (tall mode) whose two 32-row
+// halves travel as ONE item when both are full and share a constant coefficient class; a greedy pass at launch gives
+// the items to the CTAs by estimated cost (same result on every CTA).  Phase AB of a full constant-coefficient item
+// runs by warp-private rows (run_rows: p_new in registers, neighbours by shuffle, no barrier between the p update
+// and the stencil); mixed and partial tiles take the tile path (run_tile: p update in place in shared memory,
+// barrier, stencil).  Both evaluate the same expressions on the same operands.
+//
 // Replaces the same reference pieces as persistent.cu (S4:846-942, kernels S4:507-676).
 #include <type_traits>
 
